@@ -1,0 +1,213 @@
+"""Host-side stand-in for the LAMMPS machinery on either side of the pair style:
+synthetic water boxes, periodic ghost atoms, full/half neighbour lists at cutoff+skin, and the brick
+domain decomposition with its halo send/receive plan.  Used by bench.py and the tests to feed the
+C ABI exactly what `PairANI::compute` hands to `ANI::compute`
+(/root/reference/src/pair_ani.cpp:98-151): x[ntotal][3], type-1 species, ilist/numneigh/jlist.
+
+Conventions copied from LAMMPS: local atoms first (0..nlocal-1), ghosts after; a ghost is a copy of an
+owned atom displaced by a periodic image and/or owned by another rank; full list = every j within the
+list cutoff of local i (j local or ghost); half list with newton off = local-local pairs once, plus every
+local-ghost pair stored on the local atom (external/lammps/src/npair_half_bin_newtoff.cpp behaviour).
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from typing import List, Optional, Tuple
+
+import numpy as np
+
+WATER_MOLECULES_PER_A3 = 0.0334   # ~0.998 g/cc; the reference's 20k box: 7128 molecules / 60^3 A^3 = 0.0330
+LIST_CUTOFF = 7.1                 # pair cutoff 5.1 + skin 2.0 (/root/reference/tests/in.lammps:19)
+
+
+def make_water_box(cells: Tuple[int, int, int], seed: int = 12345, jitter: float = 0.25):
+    """Waters on a jittered simple-cubic lattice with uniformly random orientations
+    (the fallback generator of SURVEY.md 8d; geometry r_OH 0.9572 A, HOH 104.52 deg).
+    Returns (positions [N,3] f64, species [N] int32 with ANI-2x indices H=0,O=3, box [3])."""
+    rng = np.random.default_rng(seed)
+    a = (1.0 / WATER_MOLECULES_PER_A3) ** (1.0 / 3.0)
+    nx, ny, nz = cells
+    gx, gy, gz = np.meshgrid(np.arange(nx), np.arange(ny), np.arange(nz), indexing="ij")
+    o = (np.stack([gx, gy, gz], -1).reshape(-1, 3) + 0.5) * a
+    nmol = o.shape[0]
+    o = o + rng.uniform(-jitter, jitter, size=o.shape)
+    # random rotations from unit quaternions
+    q = rng.standard_normal((nmol, 4))
+    q /= np.linalg.norm(q, axis=1, keepdims=True)
+    w, x, y, z = q.T
+    R = np.stack([
+        np.stack([1 - 2 * (y * y + z * z), 2 * (x * y - z * w), 2 * (x * z + y * w)], -1),
+        np.stack([2 * (x * y + z * w), 1 - 2 * (x * x + z * z), 2 * (y * z - x * w)], -1),
+        np.stack([2 * (x * z - y * w), 2 * (y * z + x * w), 1 - 2 * (x * x + y * y)], -1)], 1)
+    r_oh, ang = 0.9572, np.deg2rad(104.52)
+    h1 = np.array([r_oh * np.sin(ang / 2), 0.0, r_oh * np.cos(ang / 2)])
+    h2 = np.array([-r_oh * np.sin(ang / 2), 0.0, r_oh * np.cos(ang / 2)])
+    H1 = o + R @ h1
+    H2 = o + R @ h2
+    pos = np.stack([o, H1, H2], 1).reshape(-1, 3)
+    species = np.tile(np.array([3, 0, 0], dtype=np.int32), nmol)
+    box = np.array([nx, ny, nz], dtype=np.float64) * a
+    pos = np.mod(pos, box)
+    return pos, species, box
+
+
+def cells_for_atoms(natoms: int) -> Tuple[int, int, int]:
+    """Near-cubic lattice whose atom count is close to `natoms` (3 atoms per cell)."""
+    nmol = max(1, natoms // 3)
+    n = max(1, round(nmol ** (1.0 / 3.0)))
+    best = None
+    for nx in range(max(1, n - 3), n + 4):
+        for ny in range(max(1, n - 3), n + 4):
+            nz = max(1, round(nmol / (nx * ny)))
+            err = abs(nx * ny * nz - nmol) + 0.01 * (abs(nx - ny) + abs(ny - nz))
+            if best is None or err < best[0]:
+                best = (err, (nx, ny, nz))
+    return best[1]
+
+
+@dataclass
+class Subdomain:
+    """What one MPI rank of LAMMPS holds for the pair style."""
+    nlocal: int
+    x: np.ndarray                 # [ntotal,3] f64, locals then ghosts
+    species: np.ndarray           # [ntotal] int32 (type-1)
+    ghost_owner_rank: np.ndarray  # [nghost] rank owning the real atom
+    ghost_owner_index: np.ndarray  # [nghost] local index on the owner
+    global_id: np.ndarray         # [ntotal] id in the global box
+    lo: np.ndarray
+    hi: np.ndarray
+
+    @property
+    def ntotal(self) -> int:
+        return self.x.shape[0]
+
+    @property
+    def nghost(self) -> int:
+        return self.ntotal - self.nlocal
+
+
+def _ghost_images(pos, box, lo, hi, cut, periodic=True):
+    """All images (including shift 0 for atoms outside [lo,hi)) of `pos` inside the halo shell of the brick
+    [lo-cut, hi+cut) minus the brick itself.  Returns (index into pos, shifted coordinates)."""
+    idx_all, x_all = [], []
+    rng = [-1, 0, 1] if periodic else [0]
+    # enough images when box >= cut; for tiny boxes (8 A box, 7.1 A halo) allow +-ceil(cut/box) images
+    reach = [int(np.ceil(cut / b)) if periodic else 0 for b in box]
+    for sx in range(-reach[0], reach[0] + 1):
+        for sy in range(-reach[1], reach[1] + 1):
+            for sz in range(-reach[2], reach[2] + 1):
+                shift = np.array([sx, sy, sz]) * box
+                y = pos + shift
+                inside_halo = np.all((y >= lo - cut) & (y < hi + cut), axis=1)
+                inside_brick = np.all((y >= lo) & (y < hi), axis=1)
+                sel = np.nonzero(inside_halo & ~inside_brick)[0]
+                if sel.size:
+                    idx_all.append(sel)
+                    x_all.append(y[sel])
+    if not idx_all:
+        return np.zeros(0, dtype=np.int64), np.zeros((0, 3))
+    return np.concatenate(idx_all), np.concatenate(x_all)
+
+
+def decompose(pos, species, box, grid=(1, 1, 1), cut: float = LIST_CUTOFF, periodic: bool = True) -> List[Subdomain]:
+    """Brick decomposition of a periodic box onto px*py*pz ranks (rank = ix*py*pz + iy*pz + iz) with the
+    cut-wide halo LAMMPS' Comm::borders would create (comm_brick.cpp:771-)."""
+    pos = np.asarray(pos, dtype=np.float64)
+    grid = np.asarray(grid)
+    cell = box / grid
+    owner_cell = np.minimum((pos / cell).astype(np.int64), grid - 1)
+    owner_rank = (owner_cell[:, 0] * grid[1] + owner_cell[:, 1]) * grid[2] + owner_cell[:, 2]
+    nranks = int(np.prod(grid))
+    local_ids = [np.nonzero(owner_rank == r)[0] for r in range(nranks)]
+    local_index = np.empty(pos.shape[0], dtype=np.int64)
+    for ids in local_ids:
+        local_index[ids] = np.arange(ids.size)
+    out = []
+    for r in range(nranks):
+        ix, rem = divmod(r, grid[1] * grid[2])
+        iy, iz = divmod(rem, grid[2])
+        lo = np.array([ix, iy, iz]) * cell
+        hi = lo + cell
+        ids = local_ids[r]
+        gidx, gx = _ghost_images(pos, box, lo, hi, cut, periodic)
+        x = np.concatenate([pos[ids], gx])
+        sp = np.concatenate([species[ids], species[gidx]]).astype(np.int32)
+        out.append(Subdomain(nlocal=ids.size, x=x, species=sp, ghost_owner_rank=owner_rank[gidx],
+                             ghost_owner_index=local_index[gidx], global_id=np.concatenate([ids, gidx]),
+                             lo=lo, hi=hi))
+    return out
+
+
+def full_neighbor_list(x, nlocal: int, cut: float = LIST_CUTOFF):
+    """LAMMPS-style full list for local atoms over local+ghost coordinates.
+    Returns (ilist [nlocal] i32, numneigh [nlocal] i32, jlist [P] i32 flattened in ilist order)."""
+    from scipy.spatial import cKDTree
+    x = np.asarray(x, dtype=np.float64)
+    tree = cKDTree(x)
+    pairs = tree.query_pairs(cut, output_type="ndarray")  # i<j, all atoms
+    a = np.concatenate([pairs[:, 0], pairs[:, 1]])
+    b = np.concatenate([pairs[:, 1], pairs[:, 0]])
+    keep = a < nlocal
+    a, b = a[keep], b[keep]
+    order = np.lexsort((b, a))
+    a, b = a[order], b[order]
+    numneigh = np.bincount(a, minlength=nlocal).astype(np.int32)
+    return np.arange(nlocal, dtype=np.int32), numneigh, b.astype(np.int32)
+
+
+def half_neighbor_list(x, nlocal: int, cut: float = LIST_CUTOFF):
+    """Half list with newton off: int64[2][P] as `atom_index12` (pair_ani.cpp:143-146): local-local pairs
+    once (i<j), local-ghost pairs stored with the local atom first."""
+    from scipy.spatial import cKDTree
+    x = np.asarray(x, dtype=np.float64)
+    pairs = cKDTree(x).query_pairs(cut, output_type="ndarray")
+    keep = pairs[:, 0] < nlocal            # i<j and locals come first => i local covers all needed pairs
+    p = pairs[keep]
+    order = np.lexsort((p[:, 1], p[:, 0]))
+    p = p[order]
+    return np.ascontiguousarray(p.T.astype(np.int64))
+
+
+def fold_ghost_forces(sub: Subdomain, forces: np.ndarray) -> np.ndarray:
+    """Single-rank reverse communication (pair_ani.cpp:197-201,461-484): add each ghost's force onto its owner."""
+    f = np.array(forces[:sub.nlocal], dtype=np.float64, copy=True)
+    np.add.at(f, sub.ghost_owner_index, forces[sub.nlocal:])
+    return f
+
+
+@dataclass
+class HaloPlan:
+    """Per-rank send/recv description for the forward (positions) and reverse (forces) exchanges.
+    send_index[r]: local atom indices whose coordinates (plus send_shift[r]) rank r needs as ghosts;
+    recv_slice[r]: where, inside this rank's ghost block, the atoms received from rank r land."""
+    send_index: List[np.ndarray]
+    send_shift: List[np.ndarray]
+    recv_start: List[int]
+    recv_count: List[int]
+
+
+def halo_plans(subs: List[Subdomain], pos_global: np.ndarray) -> List[HaloPlan]:
+    """Build all ranks' plans at once (host setup; in LAMMPS this is Comm::borders)."""
+    n = len(subs)
+    # order every rank's ghosts by owner rank so each peer's block is contiguous
+    for s in subs:
+        order = np.argsort(s.ghost_owner_rank, kind="stable")
+        nl = s.nlocal
+        s.x[nl:] = s.x[nl:][order]
+        s.species[nl:] = s.species[nl:][order]
+        s.global_id[nl:] = s.global_id[nl:][order]
+        s.ghost_owner_rank = s.ghost_owner_rank[order]
+        s.ghost_owner_index = s.ghost_owner_index[order]
+    plans = [HaloPlan([None] * n, [None] * n, [0] * n, [0] * n) for _ in range(n)]
+    for r, s in enumerate(subs):
+        counts = np.bincount(s.ghost_owner_rank, minlength=n)
+        starts = np.concatenate([[0], np.cumsum(counts)])
+        for o in range(n):
+            plans[r].recv_start[o] = int(starts[o])
+            plans[r].recv_count[o] = int(counts[o])
+            sel = slice(int(starts[o]), int(starts[o + 1]))
+            oi = s.ghost_owner_index[sel]
+            shift = s.x[s.nlocal:][sel] - subs[o].x[oi]      # image displacement seen by the receiver
+            plans[o].send_index[r] = oi.astype(np.int64)
+            plans[o].send_shift[r] = shift
+    return plans
