@@ -1,0 +1,110 @@
+/* ani_b200.h -- C ABI of libani_b200.so: B200 (sm_100a) ANI energy / force evaluation.
+ *
+ * This is the drop-in boundary for the hot path of roitberg-group/lammps-ani.  Every entry point replaces
+ * one piece of the reference's libtorch runner `class ANI` (src/ani_csrc/ani.h:11-84, ani.cpp) as it is
+ * called from the LAMMPS pair styles (src/pair_ani.cpp:66-233, src/pair_ani_kokkos.cpp:67-214).  Plain
+ * pointers and sizes only: no torch, Kokkos or LAMMPS types.  All functions return 0 on success and a
+ * non-zero code on failure; ani_last_error() then describes it (thread-local).  No exceptions cross the ABI.
+ * There is NO CPU fallback: ani_ctx_create fails when no CUDA device is usable.
+ *
+ * Units: inputs in Angstrom, outputs in kcal/mol and kcal/mol/Angstrom (model values x 627.5094738898777,
+ * reference ani.h:9, ani.cpp:161-162,246-247).
+ */
+#ifndef ANI_B200_H
+#define ANI_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ANI_B200_ABI_VERSION 1
+#define ANI_HARTREE2KCALMOL 627.5094738898777
+
+typedef struct ani_model ani_model; /* host-side parameters (one `.aniw` file)                    */
+typedef struct ani_ctx ani_ctx;     /* one device context: weights in HBM, work buffers, a stream */
+
+/* MLP arithmetic of the single-precision mode (ani_ctx_set_mlp_mode).  The default reproduces fp32. */
+enum ani_mlp_mode {
+  ANI_MLP_FP32_SIMT = 0, /* FFMA GEMMs, fp32 accumulate: the strict reference-precision path (and fp64 mode)   */
+  ANI_MLP_TF32X3 = 1,    /* tcgen05.mma kind::tf32, 3-pass hi/lo split, fp32 accumulate in TMEM (~fp32 accuracy) */
+  ANI_MLP_TF32 = 2,      /* single-pass TF32 on tcgen05 -- the reference's LAMMPS_ANI_ALLOW_TF32=1 (ani.cpp:41-43) */
+};
+
+/* ---- model parameters ------------------------------------------------------------------------------
+ * Replaces torch::jit::load + module_to_dtype (ani.cpp:13-33,46-61).  `path` is an `.aniw` blob written
+ * once by `python -m lammps_ani_b200.extract` from ani2x.pt / ani1x_nr.pt / a NeuroChem .info file.  If
+ * `path` ends in ".pt" the loader looks for "<path>.aniw" next to it and fails with instructions if absent. */
+int ani_model_load(const char* path, ani_model** out);
+void ani_model_free(ani_model* model);
+/* attrs `num_models`, AEV geometry (lammps_ani.py:104-105).  Any out pointer may be NULL. */
+int ani_model_info(const ani_model* model, int* num_species, int* aev_length, int* num_models, double* Rcr,
+                   double* Rca);
+
+/* ---- context ----------------------------------------------------------------------------------------
+ * Replaces ANI::ANI(model_file, local_rank, use_num_models, use_cuaev, use_fullnbr, use_single)
+ * (ani.h:32-37, ani.cpp:35-97): `device` = CUDA ordinal (the reference's local_rank; -1 = "cpu" is
+ * REJECTED here), use_num_models = -1 for all members (select_models, lammps_ani.py:332-343),
+ * use_cuaev: 1 = radial terms re-filtered at Rcr (cuaev behaviour), 0 = `pyaev` behaviour: every pair of
+ * the supplied list contributes a radial term; use_single: 1 fp32, 0 fp64 arithmetic. */
+int ani_ctx_create(const ani_model* model, int device, int use_num_models, int use_cuaev, int use_fullnbr,
+                   int use_single, ani_ctx** out);
+void ani_ctx_destroy(ani_ctx* ctx);
+int ani_ctx_set_mlp_mode(ani_ctx* ctx, int mode); /* enum ani_mlp_mode; single precision only */
+/* Run on the caller's CUDA stream (cudaStream_t as void*) instead of the context's own, so device-resident
+ * callers (ani/kk, the multi-GPU halo exchange) keep stream order with their own kernels / NCCL. */
+int ani_ctx_set_stream(ani_ctx* ctx, void* cuda_stream);
+int ani_ctx_synchronize(ani_ctx* ctx);
+
+/* ---- neighbour data: call when the list was rebuilt (neighbor->ago == 0, pair_ani.cpp:107-151) ---------
+ * species[ntotal] = LAMMPS type-1 for local AND ghost atoms (pair_ani.cpp:109-111).
+ * Full list (ani.cpp:213-229): ilist[inum] local atom indices, numneigh[] INDEXED BY ATOM like LAMMPS'
+ * list->numneigh, jlist = the flattened neighbours in ilist order with the special bits already masked
+ * (j &= NEIGHMASK, pair_ani.cpp:138-139), npairs = sum numneigh[ilist[ii]].
+ * Half list (ani.cpp:122-137): atom_index12 = int64[2][npairs], first row i, second row j.
+ * on_device != 0: all pointers are device pointers (ani/kk, pair_ani_kokkos.cpp:143-169).               */
+int ani_set_neighbors_full(ani_ctx* ctx, int nlocal, int ntotal, const int* species, int inum, const int* ilist,
+                           const int* numneigh, const int* jlist, int64_t npairs, int on_device);
+int ani_set_neighbors_half(ani_ctx* ctx, int nlocal, int ntotal, const int* species, int64_t npairs,
+                           const int64_t* atom_index12, int on_device);
+
+/* ---- one timestep, host arrays (plain `ani` style; ANI::compute host overloads ani.cpp:100-265) ---------
+ * x[ntotal][3] doubles.  out_energy: sum over LOCAL atoms.  out_force[ntotal][3] is OVERWRITTEN with the
+ * force on local and ghost atoms (the caller folds ghosts back: pair_ani.cpp:197-210).  out_eatom[nlocal]
+ * may be NULL (eflag_atom off).  out_virial9 (3x3 row major) may be NULL (vflag off); unlike cuaev, which
+ * returns zeros (lammps_ani.py:151-153,208-211), it is always the true -sym(sum dE/dd (x) d).            */
+int ani_compute(ani_ctx* ctx, const double* x, double* out_energy, double* out_force, double* out_eatom,
+                double* out_virial9);
+
+/* ---- one timestep, device arrays (`ani/kk`; ANI::compute tensor overload ani.cpp:268-316) -----------------
+ * x_dev: [ntotal][3] of double (x_is_float=0) or float (1).  f_dev: [ntotal][3] double/float, ACCUMULATED in
+ * place (f += force, pair_ani_kokkos.cpp:190-191).  eatom_dev: double[nlocal] accumulated, or NULL.
+ * out_energy / out_virial9 are HOST pointers (may be NULL to skip the read-back and its sync).           */
+int ani_compute_device(ani_ctx* ctx, const void* x_dev, int x_is_float, void* f_dev, int f_is_float,
+                       double* eatom_dev, double* out_energy, double* out_virial9);
+
+/* ---- halo helpers for the domain-decomposed driver (CommBrick forward_comm / reverse_comm(Pair*),
+ * comm_brick.cpp:538-593,1023-1053; pair_ani.cpp:461-484) -- device pack / unpack, T = float or double.   */
+int ani_halo_pack_x(ani_ctx* ctx, const void* x_dev, int is_float, const int64_t* send_index_dev, const void* shift_dev,
+                    int64_t n, void* out_dev);
+int ani_halo_unpack_add_f(ani_ctx* ctx, void* f_dev, int is_float, const int64_t* index_dev, const void* buf_dev,
+                          int64_t n);
+
+/* ---- introspection for tests, profiling and bench ------------------------------------------------------- */
+/* Copy the AEV rows / dE/dAEV rows of the local atoms (atom order, [nlocal][aev_length] doubles) of the
+ * last compute to host memory. */
+int ani_debug_get_aev(ani_ctx* ctx, double* out_aev, double* out_daev);
+/* Device time (ms, CUDA events on the context's stream) of the stages of the last compute:
+ * [0] pack/H2D, [1] AEV forward, [2] MLP forward+backward, [3] AEV backward / force scatter, [4] reduce/D2H,
+ * and the number of kernels launched in that compute. */
+int ani_last_timing(ani_ctx* ctx, float stage_ms[5], int* num_launches);
+int ani_ctx_enable_timing(ani_ctx* ctx, int on);
+
+const char* ani_last_error(void);
+int ani_abi_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ANI_B200_H */

@@ -1,0 +1,726 @@
+// ani_b200.cu -- context, per-timestep orchestration and the C ABI (include/ani_b200.h) of libani_b200.so.
+//
+// Replaces the reference's libtorch runner `class ANI` (src/ani_csrc/ani.{h,cpp}) and the TorchScript step
+// graph `LammpsANI.forward` (models/lammps_ani.py:131-216).  One context = one GPU, one stream, weights and all
+// work buffers resident in HBM; per step: pack coordinates -> AEV forward -> per-species ensemble MLP forward
+// + dE/dAEV backward -> AEV backward / force + virial scatter -> energy reduction.
+#include <algorithm>
+#include <cmath>
+#include <cstdlib>
+#include <cstring>
+#include <memory>
+#include <mutex>
+
+#include "../../include/ani_b200.h"
+#include "aev.cuh"
+#include "common.cuh"
+#include "misc.cuh"
+#include "mlp_simt.cuh"
+#include "mlp_tc.cuh"
+
+namespace anib {
+
+static thread_local std::string g_last_error;
+void set_error(const std::string& msg) { g_last_error = msg; }
+
+struct DevBuf {
+  void* p = nullptr;
+  size_t cap = 0;
+  ~DevBuf() { if (p) cudaFree(p); }
+  // grow-only; returns false on allocation failure
+  bool reserve(size_t bytes) {
+    if (bytes <= cap) return true;
+    if (p) { cudaFree(p); p = nullptr; cap = 0; }
+    size_t want = bytes + bytes / 8 + 256;
+    if (cudaMalloc(&p, want) != cudaSuccess) { p = nullptr; return false; }
+    cap = want;
+    return true;
+  }
+  template <typename U> U* as() const { return (U*)p; }
+};
+
+struct PinnedBuf {
+  void* p = nullptr;
+  size_t cap = 0;
+  ~PinnedBuf() { if (p) cudaFreeHost(p); }
+  bool reserve(size_t bytes) {
+    if (bytes <= cap) return true;
+    if (p) { cudaFreeHost(p); p = nullptr; cap = 0; }
+    size_t want = bytes + bytes / 8 + 256;
+    if (cudaMallocHost(&p, want) != cudaSuccess) { p = nullptr; return false; }
+    cap = want;
+    return true;
+  }
+  template <typename U> U* as() const { return (U*)p; }
+};
+
+#define ANIB_RESERVE(buf, bytes)                                                                              \
+  do {                                                                                                        \
+    if (!(buf).reserve(bytes)) {                                                                              \
+      set_error(std::string("out of memory reserving ") + std::to_string((size_t)(bytes)) + " bytes for " #buf); \
+      return 1;                                                                                               \
+    }                                                                                                         \
+  } while (0)
+
+struct EngineBase {
+  virtual ~EngineBase() {}
+  virtual int set_neighbors(int nlocal, int ntotal, const int* species_h, const int64_t* beg_h, const int* cnt_h,
+                            const int* jlist, int64_t npairs, bool jlist_on_device) = 0;
+  virtual int compute(const void* x, bool x_on_device, bool x_is_float, double* out_energy, double* out_force_host,
+                      void* f_dev, bool f_is_float, double* out_eatom_host, double* eatom_dev, double* out_virial9) = 0;
+  virtual int get_aev(double* aev, double* daev) = 0;
+};
+
+template <typename T>
+struct SpeciesNet {
+  int nl = 0;                 // number of linear layers (hidden + output)
+  std::vector<int> dims;      // in, h1, ..., 1
+  std::vector<DevBuf> W, b;   // [l]: [M][out][in], [M][out]   (l < nl-1: hidden; l == nl-1: output row w4[M][h], b4[M])
+  std::vector<DevBuf> WT;     // [l] (1 <= l < nl-1): [M][in][out]  (operand of the backward GEMMs)
+  DevBuf W1cat;               // [L][M*h1]: W1cat[n][m*h1+k] = W1_m[k][n]
+  TcSpeciesWeights tc;        // TF32 hi/lo planes for the tcgen05 path (fp32 only)
+};
+
+}  // namespace anib
+
+using namespace anib;
+
+struct ani_model {
+  HostModel hm;
+};
+
+struct ani_ctx {
+  int device = 0;
+  bool use_single = true, use_cuaev = true, use_fullnbr = true;
+  int num_models = 0;
+  int mlp_mode = ANI_MLP_FP32_SIMT;
+  cudaStream_t stream = nullptr, own_stream = nullptr;
+  bool timing = false;
+  cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+  float stage_ms[5] = {0, 0, 0, 0, 0};
+  int launches = 0;
+  const HostModel* hm = nullptr;
+  std::unique_ptr<EngineBase> eng;
+  // host scratch for list conversion
+  std::vector<int64_t> h_beg;
+  std::vector<int> h_cnt, h_species, h_tmp;
+  std::vector<int> h_jl;
+};
+
+namespace anib {
+
+template <typename T>
+struct Engine : EngineBase {
+  ani_ctx* c;
+  const HostModel& hm;
+  int M;   // members in use
+  AevConst<T> P;
+  std::vector<SpeciesNet<T>> nets;
+  // per-rebuild state
+  int nlocal = 0, ntotal = 0, cap = 32, capA = 64;
+  int64_t npairs = 0;
+  std::vector<int> boff;   // bucket offsets [S+1] (rows of species s = [boff[s], boff[s+1]))
+  std::vector<int> h_order;
+  DevBuf d_species, d_beg, d_cnt, d_jlist, d_order;
+  const int* jlist_ptr = nullptr;
+  // per-step state
+  DevBuf d_xraw, d_x4, d_aev, d_daev, d_force, d_eatom, d_eatom_atom, d_partial, d_scalars, d_virial, d_err;
+  DevBuf d_aev_hi, d_aev_lo;
+  DevBuf d_H, d_D, d_G;   // MLP intermediates of one chunk
+  TcWork tcw;
+  PinnedBuf h_x, h_f, h_small;
+  int64_t ld_aev = 0;
+  int chunk_rows = 2048;
+
+  Engine(ani_ctx* ctx, const HostModel& m, int M_) : c(ctx), hm(m), M(M_) {
+    const char* e = getenv("ANI_B200_MLP_CHUNK");
+    if (e && atoi(e) > 0) chunk_rows = atoi(e);
+  }
+
+  int init() {
+    memset(&P, 0, sizeof(P));
+    P.Rcr = (T)hm.Rcr; P.Rca = (T)hm.Rca; P.Rcr2 = (T)(hm.Rcr * hm.Rcr); P.Rca2 = (T)(hm.Rca * hm.Rca);
+    P.EtaR = (T)hm.EtaR; P.EtaA = (T)hm.EtaA; P.Zeta = (T)hm.Zeta;
+    P.pi_over_Rcr = (T)(M_PI / hm.Rcr); P.pi_over_Rca = (T)(M_PI / hm.Rca);
+    for (int k = 0; k < hm.nR; k++) P.ShfR[k] = (T)hm.ShfR[k];
+    for (int k = 0; k < hm.nA; k++) P.ShfA[k] = (T)hm.ShfA[k];
+    for (int k = 0; k < hm.nZ; k++) { P.cosZ[k] = (T)cos(hm.ShfZ[k]); P.sinZ[k] = (T)sin(hm.ShfZ[k]); }
+    P.S = hm.S; P.nR = hm.nR; P.nA = hm.nA; P.nZ = hm.nZ;
+    P.rad_len = hm.rad_len(); P.ang_sub = hm.ang_sub(); P.aev_len = hm.aev_len(); P.npairs = hm.S * (hm.S + 1) / 2;
+    if (P.ang_sub > 32) { set_error("nShfA*nShfZ > 32 is not supported by the angular kernels"); return 1; }
+    int p = 0;
+    for (int s = 0; s < hm.S; s++)
+      for (int t = s; t < hm.S; t++) { P.triu[s][t] = p; P.triu[t][s] = p; p++; }
+    ld_aev = (P.aev_len + 3) / 4 * 4;
+    // ---- upload weights in the arithmetic type
+    nets.resize(hm.S);
+    for (int s = 0; s < hm.S; s++) {
+      SpeciesNet<T>& n = nets[s];
+      n.dims = hm.dims[s];
+      n.nl = (int)n.dims.size() - 1;
+      n.W.resize(n.nl); n.b.resize(n.nl); n.WT.resize(n.nl);
+      for (int l = 0; l < n.nl; l++) {
+        const int ni = n.dims[l], no = n.dims[l + 1];
+        std::vector<T> w((size_t)M * no * ni), bb((size_t)M * no);
+        for (int m = 0; m < M; m++) {
+          for (size_t q = 0; q < (size_t)no * ni; q++) w[(size_t)m * no * ni + q] = (T)hm.W[m][s][l][q];
+          for (int q = 0; q < no; q++) bb[(size_t)m * no + q] = (T)hm.b[m][s][l][q];
+        }
+        ANIB_RESERVE(n.W[l], w.size() * sizeof(T));
+        ANIB_RESERVE(n.b[l], bb.size() * sizeof(T));
+        ANIB_CUDA_OK(cudaMemcpy(n.W[l].p, w.data(), w.size() * sizeof(T), cudaMemcpyHostToDevice));
+        ANIB_CUDA_OK(cudaMemcpy(n.b[l].p, bb.data(), bb.size() * sizeof(T), cudaMemcpyHostToDevice));
+        if (l >= 1 && l < n.nl - 1) {
+          std::vector<T> wt((size_t)M * ni * no);
+          for (int m = 0; m < M; m++)
+            for (int o = 0; o < no; o++)
+              for (int k = 0; k < ni; k++)
+                wt[((size_t)m * ni + k) * no + o] = (T)hm.W[m][s][l][(size_t)o * ni + k];
+          ANIB_RESERVE(n.WT[l], wt.size() * sizeof(T));
+          ANIB_CUDA_OK(cudaMemcpy(n.WT[l].p, wt.data(), wt.size() * sizeof(T), cudaMemcpyHostToDevice));
+        }
+      }
+      {
+        const int L = n.dims[0], h1 = n.dims[1];
+        std::vector<T> cat((size_t)L * M * h1);
+        for (int m = 0; m < M; m++)
+          for (int k = 0; k < h1; k++)
+            for (int q = 0; q < L; q++) cat[(size_t)q * M * h1 + (size_t)m * h1 + k] = (T)hm.W[m][s][0][(size_t)k * L + q];
+        ANIB_RESERVE(n.W1cat, cat.size() * sizeof(T));
+        ANIB_CUDA_OK(cudaMemcpy(n.W1cat.p, cat.data(), cat.size() * sizeof(T), cudaMemcpyHostToDevice));
+      }
+    }
+    ANIB_RESERVE(d_err, sizeof(int));
+    ANIB_CUDA_OK(cudaMemset(d_err.p, 0, sizeof(int)));
+    ANIB_RESERVE(d_scalars, 16 * sizeof(double));
+    ANIB_RESERVE(d_virial, kVirialSlots * 9 * sizeof(double));
+    ANIB_RESERVE(d_partial, 1024 * sizeof(double));
+    return 0;
+  }
+
+  // ---------------------------------------------------------------------------------------------- rebuild
+  int set_neighbors(int nlocal_, int ntotal_, const int* species_h, const int64_t* beg_h, const int* cnt_h,
+                    const int* jlist, int64_t npairs_, bool jlist_on_device) override {
+    nlocal = nlocal_; ntotal = ntotal_; npairs = npairs_;
+    cudaStream_t st = c->stream;
+    // species bucketing (stable counting sort over local atoms) -- K4 of SURVEY.md 2.1, on rebuild only
+    boff.assign(hm.S + 1, 0);
+    for (int i = 0; i < nlocal; i++) {
+      int s = species_h[i];
+      if (s < 0 || s >= hm.S) { set_error("atom " + std::to_string(i) + " has species index " + std::to_string(s) + " outside the model's species"); return 1; }
+      boff[s + 1]++;
+    }
+    for (int i = nlocal; i < ntotal; i++)
+      if (species_h[i] < 0 || species_h[i] >= hm.S) { set_error("ghost atom has a species index outside the model's species"); return 1; }
+    for (int s = 0; s < hm.S; s++) boff[s + 1] += boff[s];
+    h_order.resize(nlocal);
+    {
+      std::vector<int> cur(boff.begin(), boff.end() - 1);
+      for (int i = 0; i < nlocal; i++) h_order[cur[species_h[i]]++] = i;
+    }
+    int maxnn = 0;
+    for (int i = 0; i < nlocal; i++) maxnn = std::max(maxnn, cnt_h[i]);
+    cap = std::max(32, (maxnn + 31) / 32 * 32);
+    capA = std::min(cap, 96);
+    ANIB_RESERVE(d_species, (size_t)ntotal * sizeof(int));
+    ANIB_RESERVE(d_beg, (size_t)std::max(nlocal, 1) * sizeof(int64_t));
+    ANIB_RESERVE(d_cnt, (size_t)std::max(nlocal, 1) * sizeof(int));
+    ANIB_RESERVE(d_order, (size_t)std::max(nlocal, 1) * sizeof(int));
+    ANIB_RESERVE(d_jlist, (size_t)std::max<int64_t>(npairs, 1) * sizeof(int));
+    ANIB_CUDA_OK(cudaMemcpyAsync(d_species.p, species_h, (size_t)ntotal * sizeof(int), cudaMemcpyHostToDevice, st));
+    ANIB_CUDA_OK(cudaMemcpyAsync(d_beg.p, beg_h, (size_t)nlocal * sizeof(int64_t), cudaMemcpyHostToDevice, st));
+    ANIB_CUDA_OK(cudaMemcpyAsync(d_cnt.p, cnt_h, (size_t)nlocal * sizeof(int), cudaMemcpyHostToDevice, st));
+    ANIB_CUDA_OK(cudaMemcpyAsync(d_order.p, h_order.data(), (size_t)nlocal * sizeof(int), cudaMemcpyHostToDevice, st));
+    ANIB_CUDA_OK(cudaMemcpyAsync(d_jlist.p, jlist, (size_t)npairs * sizeof(int),
+                                 jlist_on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, st));
+    ANIB_CUDA_OK(cudaStreamSynchronize(st));   // host staging vectors may be reused by the caller
+    // per-step buffers
+    ANIB_RESERVE(d_x4, (size_t)std::max(ntotal, 1) * 4 * sizeof(T));
+    ANIB_RESERVE(d_xraw, (size_t)std::max(ntotal, 1) * 3 * sizeof(double));
+    ANIB_RESERVE(d_force, (size_t)std::max(ntotal, 1) * 3 * sizeof(T));
+    ANIB_RESERVE(d_aev, (size_t)std::max(nlocal, 1) * ld_aev * sizeof(T));
+    ANIB_RESERVE(d_daev, (size_t)std::max(nlocal, 1) * ld_aev * sizeof(T));
+    ANIB_RESERVE(d_eatom, (size_t)std::max(nlocal, 1) * sizeof(double));
+    ANIB_RESERVE(d_eatom_atom, (size_t)std::max(nlocal, 1) * sizeof(double));
+    return 0;
+  }
+
+  // ---------------------------------------------------------------------------------------------- MLP (SIMT)
+  template <int EPI>
+  void gemm(int R, int N, int K, const T* A, int64_t lda, int64_t sAz, const T* B, int64_t ldb, int64_t sBz, T* C,
+            int64_t ldc, int64_t sCz, T* C2, const T* bias, int64_t sbz, const T* aux, int64_t ldx, int64_t sXz, T scale,
+            int batch) {
+    dim3 grid((N + 63) / 64, (R + 63) / 64, batch);
+    gemm_nt_kernel<T, EPI><<<grid, 256, 0, c->stream>>>(R, N, K, A, lda, sAz, B, ldb, sBz, C, ldc, sCz, C2, bias, sbz, aux,
+                                                        ldx, sXz, scale);
+    c->launches++;
+  }
+
+  int mlp_simt_species(int s, int row0, int R) {
+    SpeciesNet<T>& n = nets[s];
+    const int nh = n.nl - 1;   // hidden layers
+    // column offsets of each hidden layer inside one row of the [R][sum_l M*w_l] intermediates
+    std::vector<int64_t> coff(nh + 1, 0);
+    for (int l = 0; l < nh; l++) coff[l + 1] = coff[l] + (int64_t)M * n.dims[l + 1];
+    const int64_t rowsz = coff[nh];
+    ANIB_RESERVE(d_H, (size_t)chunk_rows * rowsz * sizeof(T));
+    ANIB_RESERVE(d_D, (size_t)chunk_rows * rowsz * sizeof(T));
+    ANIB_RESERVE(d_G, (size_t)chunk_rows * rowsz * sizeof(T));
+    for (int r0 = 0; r0 < R; r0 += chunk_rows) {
+      const int Rc = std::min(chunk_rows, R - r0);
+      const T* aev = d_aev.as<T>() + (size_t)(row0 + r0) * ld_aev;
+      T* daev = d_daev.as<T>() + (size_t)(row0 + r0) * ld_aev;
+      // buffers are laid out layer after layer: layer l block = [Rc][M][w_l]
+      auto Hl = [&](int l) { return d_H.as<T>() + (size_t)chunk_rows * coff[l]; };
+      auto Dl = [&](int l) { return d_D.as<T>() + (size_t)chunk_rows * coff[l]; };
+      auto Gl = [&](int l) { return d_G.as<T>() + (size_t)chunk_rows * coff[l]; };
+      // forward hidden layers
+      for (int l = 0; l < nh; l++) {
+        const int ni = n.dims[l], no = n.dims[l + 1];
+        const T* A = (l == 0) ? aev : Hl(l - 1);
+        const int64_t lda = (l == 0) ? ld_aev : (int64_t)M * ni;
+        const int64_t sAz = (l == 0) ? 0 : ni;
+        gemm<EPI_BIAS_CELU>(Rc, no, ni, A, lda, sAz, n.W[l].template as<T>(), ni, (int64_t)no * ni, Hl(l), (int64_t)M * no, no,
+                            Dl(l), n.b[l].template as<T>(), no, nullptr, 0, 0, T(1), M);
+      }
+      // output layer + dE/dz of the last hidden layer
+      {
+        const int h = n.dims[nh];
+        mlp_out_kernel<T><<<(Rc + 3) / 4, 128, 0, c->stream>>>(Rc, M, h, Hl(nh - 1), Dl(nh - 1), n.W[nh].template as<T>(),
+                                                              n.b[nh].template as<T>(), Gl(nh - 1),
+                                                              d_eatom.as<double>() + row0 + r0, hm.sae[s]);
+        c->launches++;
+      }
+      // backward through hidden layers nh-1 .. 1
+      for (int l = nh - 1; l >= 1; l--) {
+        const int ni = n.dims[l], no = n.dims[l + 1];   // layer l maps ni -> no; gradient goes no -> ni
+        gemm<EPI_MUL_AUX>(Rc, ni, no, Gl(l), (int64_t)M * no, no, n.WT[l].template as<T>(), no, (int64_t)ni * no, Gl(l - 1),
+                          (int64_t)M * ni, ni, nullptr, nullptr, 0, Dl(l - 1), (int64_t)M * ni, ni, T(1), M);
+      }
+      // dE/dAEV with the ensemble mean folded into K
+      {
+        const int h1 = n.dims[1];
+        gemm<EPI_SCALE>(Rc, n.dims[0], M * h1, Gl(0), (int64_t)M * h1, 0, n.W1cat.template as<T>(), (int64_t)M * h1, 0, daev,
+                        ld_aev, 0, nullptr, nullptr, 0, nullptr, 0, 0, T(1) / T(M), 1);
+      }
+    }
+    return 0;
+  }
+
+  int mlp_tc_species(int s, int row0, int R);   // defined for float below
+
+  // ---------------------------------------------------------------------------------------------- one step
+  int compute(const void* x, bool x_on_device, bool x_is_float, double* out_energy, double* out_force_host, void* f_dev,
+              bool f_is_float, double* out_eatom_host, double* eatom_dev, double* out_virial9) override {
+    cudaStream_t st = c->stream;
+    c->launches = 0;
+    const bool tm = c->timing;
+    if (tm) cudaEventRecord(c->ev[0], st);
+    // ---- (0) coordinates
+    const void* xsrc = x;
+    if (!x_on_device) {
+      const size_t bytes = (size_t)ntotal * 3 * sizeof(double);
+      ANIB_RESERVE(h_x, bytes);
+      memcpy(h_x.p, x, bytes);   // pageable LAMMPS array -> pinned staging
+      ANIB_CUDA_OK(cudaMemcpyAsync(d_xraw.p, h_x.p, bytes, cudaMemcpyHostToDevice, st));
+      xsrc = d_xraw.p;
+      x_is_float = false;
+    }
+    using V4 = typename Vec4T<T>::type;
+    if (ntotal > 0) {
+      pack_x_kernel<T><<<(ntotal + 255) / 256, 256, 0, st>>>(xsrc, x_is_float ? 1 : 0, d_species.as<int>(), ntotal,
+                                                             d_x4.as<V4>());
+      c->launches++;
+    }
+    ANIB_CUDA_OK(cudaMemsetAsync(d_force.p, 0, (size_t)ntotal * 3 * sizeof(T), st));
+    const bool want_virial = out_virial9 != nullptr;
+    if (want_virial) ANIB_CUDA_OK(cudaMemsetAsync(d_virial.p, 0, kVirialSlots * 9 * sizeof(double), st));
+    if (tm) cudaEventRecord(c->ev[1], st);
+    // ---- (1) AEV forward
+    const bool tc_mode = (sizeof(T) == 4) && c->mlp_mode != ANI_MLP_FP32_SIMT;
+    const int npl = 32 / (P.nR <= 16 ? 16 : 32);
+    if (nlocal > 0) {
+      const int acc_f = P.aev_len + (npl - 1) * P.rad_len;
+      AevSmemLayout Lf = aev_smem_layout<T>(cap, capA, acc_f, false);
+      const int smem = Lf.bytes * kAevWarps;
+      ANIB_CUDA_OK(cudaFuncSetAttribute(aev_forward_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+      float *hi = nullptr, *lo = nullptr;
+      if (tc_mode) {
+        ANIB_RESERVE(d_aev_hi, (size_t)tc_padded_rows(nlocal, hm.S) * ld_aev * sizeof(float));
+        ANIB_RESERVE(d_aev_lo, (size_t)tc_padded_rows(nlocal, hm.S) * ld_aev * sizeof(float));
+        hi = d_aev_hi.as<float>(); lo = d_aev_lo.as<float>();
+      }
+      aev_forward_kernel<T><<<(nlocal + kAevWarps - 1) / kAevWarps, kAevWarps * 32, smem, st>>>(
+          P, c->use_cuaev ? 1 : 0, d_x4.as<V4>(), d_beg.as<int64_t>(), d_cnt.as<int>(), d_jlist.as<int>(),
+          d_order.as<int>(), nlocal, d_aev.as<T>(), ld_aev, hi, lo, ld_aev, cap, capA, Lf.bytes, d_err.as<int>());
+      c->launches++;
+    }
+    if (tm) cudaEventRecord(c->ev[2], st);
+    // ---- (2) MLP forward + backward per species bucket
+    for (int s = 0; s < hm.S; s++) {
+      const int R = boff[s + 1] - boff[s];
+      if (R == 0) continue;
+      int rc = tc_mode ? mlp_tc_species(s, boff[s], R) : mlp_simt_species(s, boff[s], R);
+      if (rc) return rc;
+    }
+    if (tm) cudaEventRecord(c->ev[3], st);
+    // ---- (3) AEV backward: forces on local + ghost atoms, virial
+    if (nlocal > 0) {
+      const int acc_b = P.S * (P.nR + 1) + P.npairs * (P.ang_sub + 1);
+      AevSmemLayout Lb = aev_smem_layout<T>(cap, capA, acc_b, true);
+      const int smem = Lb.bytes * kAevWarps;
+      auto launch = [&](auto kern) -> int {
+        ANIB_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        kern<<<(nlocal + kAevWarps - 1) / kAevWarps, kAevWarps * 32, smem, st>>>(
+            P, c->use_cuaev ? 1 : 0, d_x4.as<V4>(), d_beg.as<int64_t>(), d_cnt.as<int>(), d_jlist.as<int>(),
+            d_order.as<int>(), nlocal, d_daev.as<T>(), ld_aev, d_force.as<T>(),
+            want_virial ? d_virial.as<double>() : nullptr, (T)kHartree2KcalMol, cap, capA, Lb.bytes);
+        c->launches++;
+        return 0;
+      };
+      int rc;
+      if (P.nZ == 4) rc = launch(aev_backward_kernel<T, 4>);
+      else if (P.nZ == 8) rc = launch(aev_backward_kernel<T, 8>);
+      else if (P.nZ == 1) rc = launch(aev_backward_kernel<T, 1>);
+      else if (P.nZ == 2) rc = launch(aev_backward_kernel<T, 2>);
+      else { set_error("unsupported number of ShfZ values (supported: 1, 2, 4, 8)"); return 1; }
+      if (rc) return rc;
+    }
+    if (tm) cudaEventRecord(c->ev[4], st);
+    // ---- (4) reductions and outputs
+    const bool want_e = out_energy != nullptr;
+    if (want_e) {
+      if (nlocal > 0) {
+        int nb = std::min(1024, (nlocal + 255) / 256);
+        reduce_sum_stage1<<<nb, 256, 0, st>>>(d_eatom.as<double>(), nlocal, d_partial.as<double>());
+        reduce_sum_stage2<<<1, 256, 0, st>>>(d_partial.as<double>(), nb, d_scalars.as<double>(), kHartree2KcalMol);
+        c->launches += 2;
+      } else {
+        ANIB_CUDA_OK(cudaMemsetAsync(d_scalars.p, 0, sizeof(double), st));
+      }
+    }
+    const bool want_eatom = (out_eatom_host != nullptr) || (eatom_dev != nullptr);
+    if (want_eatom && nlocal > 0) {
+      scatter_eatom_kernel<<<(nlocal + 255) / 256, 256, 0, st>>>(d_eatom.as<double>(), d_order.as<int>(), nlocal,
+                                                                kHartree2KcalMol,
+                                                                eatom_dev ? eatom_dev : d_eatom_atom.as<double>(),
+                                                                eatom_dev ? 1 : 0);
+      c->launches++;
+    }
+    if (f_dev != nullptr && ntotal > 0) {
+      const int64_t n3 = (int64_t)ntotal * 3;
+      if (f_is_float) axpy_kernel<T, float><<<(unsigned)((n3 + 255) / 256), 256, 0, st>>>(d_force.as<T>(), (float*)f_dev, n3);
+      else axpy_kernel<T, double><<<(unsigned)((n3 + 255) / 256), 256, 0, st>>>(d_force.as<T>(), (double*)f_dev, n3);
+      c->launches++;
+    }
+    // ---- D2H
+    const size_t small_bytes = (1 + 1 + kVirialSlots * 9) * sizeof(double);
+    ANIB_RESERVE(h_small, small_bytes);
+    double* hs = h_small.as<double>();
+    bool need_sync = false;
+    if (want_e) { ANIB_CUDA_OK(cudaMemcpyAsync(hs, d_scalars.p, sizeof(double), cudaMemcpyDeviceToHost, st)); need_sync = true; }
+    if (want_virial) {
+      ANIB_CUDA_OK(cudaMemcpyAsync(hs + 2, d_virial.p, kVirialSlots * 9 * sizeof(double), cudaMemcpyDeviceToHost, st));
+      need_sync = true;
+    }
+    ANIB_CUDA_OK(cudaMemcpyAsync(hs + 1, d_err.p, sizeof(int), cudaMemcpyDeviceToHost, st));
+    if (out_force_host != nullptr) {
+      ANIB_RESERVE(h_f, (size_t)ntotal * 3 * sizeof(T));
+      ANIB_CUDA_OK(cudaMemcpyAsync(h_f.p, d_force.p, (size_t)ntotal * 3 * sizeof(T), cudaMemcpyDeviceToHost, st));
+      need_sync = true;
+    }
+    PinnedBuf* eat = nullptr;
+    if (out_eatom_host != nullptr && nlocal > 0) {
+      ANIB_RESERVE(h_eat, (size_t)nlocal * sizeof(double));
+      ANIB_CUDA_OK(cudaMemcpyAsync(h_eat.p, d_eatom_atom.p, (size_t)nlocal * sizeof(double), cudaMemcpyDeviceToHost, st));
+      eat = &h_eat;
+      need_sync = true;
+    }
+    if (tm) { cudaEventRecord(c->ev[5], st); need_sync = true; }
+    if (need_sync) {
+      ANIB_CUDA_OK(cudaStreamSynchronize(st));
+      int err = *(int*)(hs + 1);
+      if (err) { set_error("an atom has more than " + std::to_string(capA) + " neighbours inside the angular cutoff"); return 2; }
+    }
+    ANIB_CUDA_OK(cudaGetLastError());
+    if (want_e) *out_energy = hs[0];
+    if (want_virial) {
+      double w[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+      for (int sl = 0; sl < kVirialSlots; sl++)
+        for (int q = 0; q < 9; q++) w[q] += hs[2 + sl * 9 + q];
+      for (int a = 0; a < 3; a++)
+        for (int b = 0; b < 3; b++) out_virial9[3 * a + b] = 0.5 * (w[3 * a + b] + w[3 * b + a]);
+    }
+    if (out_force_host != nullptr) {
+      const T* src = h_f.as<T>();
+      for (size_t k = 0; k < (size_t)ntotal * 3; k++) out_force_host[k] = (double)src[k];
+    }
+    if (eat) memcpy(out_eatom_host, eat->p, (size_t)nlocal * sizeof(double));
+    if (tm)
+      for (int q = 0; q < 5; q++) cudaEventElapsedTime(&c->stage_ms[q], c->ev[q], c->ev[q + 1]);
+    return 0;
+  }
+  PinnedBuf h_eat;
+
+  int get_aev(double* aev, double* daev) override {
+    ANIB_CUDA_OK(cudaStreamSynchronize(c->stream));
+    std::vector<T> tmp((size_t)nlocal * ld_aev);
+    for (int pass = 0; pass < 2; pass++) {
+      double* out = pass == 0 ? aev : daev;
+      if (!out) continue;
+      ANIB_CUDA_OK(cudaMemcpy(tmp.data(), pass == 0 ? d_aev.p : d_daev.p, tmp.size() * sizeof(T), cudaMemcpyDeviceToHost));
+      for (int pos = 0; pos < nlocal; pos++) {
+        const int i = h_order[pos];
+        for (int k = 0; k < P.aev_len; k++) out[(size_t)i * P.aev_len + k] = (double)tmp[(size_t)pos * ld_aev + k];
+      }
+    }
+    return 0;
+  }
+};
+
+template <> int Engine<double>::mlp_tc_species(int, int, int) {
+  set_error("tensor-core MLP modes are single precision only");
+  return 1;
+}
+
+template <> int Engine<float>::mlp_tc_species(int s, int row0, int R) {
+  return tc_mlp_species(c->stream, c->mlp_mode == ANI_MLP_TF32X3, nets[s].tc, tcw, M, nets[s].dims, d_aev_hi.as<float>(),
+                        d_aev_lo.as<float>(), ld_aev, row0, R, d_daev.as<float>(), d_eatom.as<double>(), hm.sae[s],
+                        &c->launches);
+}
+
+}  // namespace anib
+
+// ================================================================================================== C ABI
+extern "C" {
+
+const char* ani_last_error(void) { return g_last_error.c_str(); }
+int ani_abi_version(void) { return ANI_B200_ABI_VERSION; }
+
+int ani_model_load(const char* path, ani_model** out) {
+  if (!path || !out) { set_error("ani_model_load: null argument"); return 1; }
+  std::unique_ptr<ani_model> m(new ani_model());
+  std::string err;
+  if (!load_aniw(path, m->hm, err)) { set_error(err); return 1; }
+  *out = m.release();
+  return 0;
+}
+
+void ani_model_free(ani_model* m) { delete m; }
+
+int ani_model_info(const ani_model* m, int* num_species, int* aev_length, int* num_models, double* Rcr, double* Rca) {
+  if (!m) { set_error("ani_model_info: null model"); return 1; }
+  if (num_species) *num_species = m->hm.S;
+  if (aev_length) *aev_length = m->hm.aev_len();
+  if (num_models) *num_models = m->hm.M;
+  if (Rcr) *Rcr = m->hm.Rcr;
+  if (Rca) *Rca = m->hm.Rca;
+  return 0;
+}
+
+int ani_ctx_create(const ani_model* model, int device, int use_num_models, int use_cuaev, int use_fullnbr, int use_single,
+                   ani_ctx** out) {
+  if (!model || !out) { set_error("ani_ctx_create: null argument"); return 1; }
+  if (device < 0) {
+    set_error("device 'cpu' is not available: libani_b200 is a CUDA (sm_100a) implementation without a CPU path");
+    return 1;
+  }
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+    cudaGetLastError();
+    set_error("no CUDA device available (libani_b200 has no CPU fallback)");
+    return 1;
+  }
+  if (device >= ndev) { set_error("CUDA device ordinal out of range"); return 1; }
+  if (model->hm.use_repulsion) { set_error("models with the RepulsionXTB term are not supported yet"); return 1; }
+  ANIB_CUDA_OK(cudaSetDevice(device));
+  int M = use_num_models;
+  if (M == -1) M = model->hm.M;   // ani.cpp:75-77
+  if (M < 1 || M > model->hm.M) { set_error("use_num_models must be -1 or in 1..num_models"); return 1; }
+  std::unique_ptr<ani_ctx> c(new ani_ctx());
+  c->device = device; c->use_single = use_single != 0; c->use_cuaev = use_cuaev != 0; c->use_fullnbr = use_fullnbr != 0;
+  c->num_models = M; c->hm = &model->hm;
+  ANIB_CUDA_OK(cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking));
+  c->stream = c->own_stream;
+  for (int q = 0; q < 6; q++) ANIB_CUDA_OK(cudaEventCreate(&c->ev[q]));
+  int rc;
+  if (c->use_single) {
+    auto* e = new Engine<float>(c.get(), model->hm, M);
+    c->eng.reset(e);
+    rc = e->init();
+    if (!rc) rc = tc_prepare_weights(model->hm, M, e->nets);
+  } else {
+    auto* e = new Engine<double>(c.get(), model->hm, M);
+    c->eng.reset(e);
+    rc = e->init();
+  }
+  if (rc) return rc;
+  const char* mode = getenv("ANI_B200_MLP_MODE");
+  if (c->use_single) {
+    c->mlp_mode = ANI_MLP_FP32_SIMT;
+    if (getenv("LAMMPS_ANI_ALLOW_TF32") && atoi(getenv("LAMMPS_ANI_ALLOW_TF32")) != 0) c->mlp_mode = ANI_MLP_TF32;  // ani.cpp:41-43
+    if (mode) {
+      if (!strcmp(mode, "simt")) c->mlp_mode = ANI_MLP_FP32_SIMT;
+      else if (!strcmp(mode, "tf32x3")) c->mlp_mode = ANI_MLP_TF32X3;
+      else if (!strcmp(mode, "tf32")) c->mlp_mode = ANI_MLP_TF32;
+    }
+  }
+  *out = c.release();
+  return 0;
+}
+
+void ani_ctx_destroy(ani_ctx* c) {
+  if (!c) return;
+  cudaSetDevice(c->device);
+  c->eng.reset();
+  for (int q = 0; q < 6; q++) if (c->ev[q]) cudaEventDestroy(c->ev[q]);
+  if (c->own_stream) cudaStreamDestroy(c->own_stream);
+  delete c;
+}
+
+int ani_ctx_set_mlp_mode(ani_ctx* c, int mode) {
+  if (!c) { set_error("null context"); return 1; }
+  if (mode < 0 || mode > 2) { set_error("unknown MLP mode"); return 1; }
+  if (!c->use_single && mode != ANI_MLP_FP32_SIMT) { set_error("tensor-core MLP modes are single precision only"); return 1; }
+  c->mlp_mode = mode;
+  return 0;
+}
+
+int ani_ctx_set_stream(ani_ctx* c, void* s) {
+  if (!c) { set_error("null context"); return 1; }
+  c->stream = s ? (cudaStream_t)s : c->own_stream;
+  return 0;
+}
+
+int ani_ctx_synchronize(ani_ctx* c) {
+  if (!c) { set_error("null context"); return 1; }
+  ANIB_CUDA_OK(cudaSetDevice(c->device));
+  ANIB_CUDA_OK(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+int ani_ctx_enable_timing(ani_ctx* c, int on) {
+  if (!c) { set_error("null context"); return 1; }
+  c->timing = on != 0;
+  return 0;
+}
+
+int ani_last_timing(ani_ctx* c, float stage_ms[5], int* num_launches) {
+  if (!c) { set_error("null context"); return 1; }
+  if (stage_ms) for (int q = 0; q < 5; q++) stage_ms[q] = c->stage_ms[q];
+  if (num_launches) *num_launches = c->launches;
+  return 0;
+}
+
+// Bring (possibly device-resident) small integer arrays to the host.
+static int fetch_ints(std::vector<int>& dst, const int* src, size_t n, int on_device) {
+  dst.resize(n);
+  if (n == 0) return 0;
+  if (on_device) ANIB_CUDA_OK(cudaMemcpy(dst.data(), src, n * sizeof(int), cudaMemcpyDeviceToHost));
+  else memcpy(dst.data(), src, n * sizeof(int));
+  return 0;
+}
+
+int ani_set_neighbors_full(ani_ctx* c, int nlocal, int ntotal, const int* species, int inum, const int* ilist,
+                           const int* numneigh, const int* jlist, int64_t npairs, int on_device) {
+  if (!c || !species || (inum > 0 && (!ilist || !numneigh)) || (npairs > 0 && !jlist)) { set_error("ani_set_neighbors_full: null argument"); return 1; }
+  if (!c->use_fullnbr) { set_error("context was created for a half neighbour list"); return 1; }
+  if (nlocal < 0 || ntotal < nlocal || inum < 0 || inum > nlocal) { set_error("ani_set_neighbors_full: inconsistent sizes"); return 1; }
+  ANIB_CUDA_OK(cudaSetDevice(c->device));
+  if (fetch_ints(c->h_species, species, ntotal, on_device)) return 1;
+  std::vector<int> il, nn;
+  if (fetch_ints(il, ilist, inum, on_device)) return 1;
+  if (fetch_ints(nn, numneigh, nlocal, on_device)) return 1;
+  c->h_beg.assign(std::max(nlocal, 1), 0);
+  c->h_cnt.assign(std::max(nlocal, 1), 0);
+  int64_t run = 0;
+  for (int ii = 0; ii < inum; ii++) {
+    const int i = il[ii];
+    if (i < 0 || i >= nlocal) { set_error("ilist entry outside the local atoms"); return 1; }
+    c->h_beg[i] = run;
+    c->h_cnt[i] = nn[i];
+    run += nn[i];
+  }
+  if (run != npairs) { set_error("npairs does not match the sum of numneigh over ilist"); return 1; }
+  return c->eng->set_neighbors(nlocal, ntotal, c->h_species.data(), c->h_beg.data(), c->h_cnt.data(), jlist, npairs,
+                               on_device != 0);
+}
+
+int ani_set_neighbors_half(ani_ctx* c, int nlocal, int ntotal, const int* species, int64_t npairs,
+                           const int64_t* atom_index12, int on_device) {
+  if (!c || !species || (npairs > 0 && !atom_index12)) { set_error("ani_set_neighbors_half: null argument"); return 1; }
+  if (c->use_fullnbr) { set_error("context was created for a full neighbour list"); return 1; }
+  if (nlocal < 0 || ntotal < nlocal) { set_error("ani_set_neighbors_half: inconsistent sizes"); return 1; }
+  ANIB_CUDA_OK(cudaSetDevice(c->device));
+  if (fetch_ints(c->h_species, species, ntotal, on_device)) return 1;
+  std::vector<int64_t> idx((size_t)2 * npairs);
+  if (npairs > 0) {
+    if (on_device) ANIB_CUDA_OK(cudaMemcpy(idx.data(), atom_index12, idx.size() * sizeof(int64_t), cudaMemcpyDeviceToHost));
+    else memcpy(idx.data(), atom_index12, idx.size() * sizeof(int64_t));
+  }
+  // each stored pair (i,j) is a neighbour of i and, when j is local, of j: per-centre CSR over local atoms
+  const int64_t* I = idx.data();
+  const int64_t* J = idx.data() + npairs;
+  c->h_cnt.assign(std::max(nlocal, 1), 0);
+  for (int64_t p = 0; p < npairs; p++) {
+    if (I[p] < 0 || I[p] >= ntotal || J[p] < 0 || J[p] >= ntotal) { set_error("atom_index12 entry out of range"); return 1; }
+    if (I[p] < nlocal) c->h_cnt[I[p]]++;
+    if (J[p] < nlocal) c->h_cnt[J[p]]++;
+  }
+  c->h_beg.assign(std::max(nlocal, 1), 0);
+  int64_t run = 0;
+  for (int i = 0; i < nlocal; i++) { c->h_beg[i] = run; run += c->h_cnt[i]; }
+  c->h_jl.resize(std::max<int64_t>(run, 1));
+  std::vector<int64_t> cur(c->h_beg.begin(), c->h_beg.end());
+  for (int64_t p = 0; p < npairs; p++) {
+    if (I[p] < nlocal) c->h_jl[cur[I[p]]++] = (int)J[p];
+    if (J[p] < nlocal) c->h_jl[cur[J[p]]++] = (int)I[p];
+  }
+  return c->eng->set_neighbors(nlocal, ntotal, c->h_species.data(), c->h_beg.data(), c->h_cnt.data(), c->h_jl.data(), run,
+                               false);
+}
+
+int ani_compute(ani_ctx* c, const double* x, double* out_energy, double* out_force, double* out_eatom, double* out_virial9) {
+  if (!c || !x) { set_error("ani_compute: null argument"); return 1; }
+  ANIB_CUDA_OK(cudaSetDevice(c->device));
+  return c->eng->compute(x, false, false, out_energy, out_force, nullptr, false, out_eatom, nullptr, out_virial9);
+}
+
+int ani_compute_device(ani_ctx* c, const void* x_dev, int x_is_float, void* f_dev, int f_is_float, double* eatom_dev,
+                       double* out_energy, double* out_virial9) {
+  if (!c || !x_dev) { set_error("ani_compute_device: null argument"); return 1; }
+  ANIB_CUDA_OK(cudaSetDevice(c->device));
+  return c->eng->compute(x_dev, true, x_is_float != 0, out_energy, nullptr, f_dev, f_is_float != 0, nullptr, eatom_dev,
+                         out_virial9);
+}
+
+int ani_debug_get_aev(ani_ctx* c, double* aev, double* daev) {
+  if (!c) { set_error("null context"); return 1; }
+  ANIB_CUDA_OK(cudaSetDevice(c->device));
+  return c->eng->get_aev(aev, daev);
+}
+
+int ani_halo_pack_x(ani_ctx* c, const void* x_dev, int is_float, const int64_t* send_index_dev, const void* shift_dev,
+                    int64_t n, void* out_dev) {
+  if (!c) { set_error("null context"); return 1; }
+  if (n <= 0) return 0;
+  ANIB_CUDA_OK(cudaSetDevice(c->device));
+  unsigned g = (unsigned)((n * 3 + 255) / 256);
+  if (is_float) halo_pack_kernel<float><<<g, 256, 0, c->stream>>>((const float*)x_dev, send_index_dev, (const float*)shift_dev, n, (float*)out_dev);
+  else halo_pack_kernel<double><<<g, 256, 0, c->stream>>>((const double*)x_dev, send_index_dev, (const double*)shift_dev, n, (double*)out_dev);
+  ANIB_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+int ani_halo_unpack_add_f(ani_ctx* c, void* f_dev, int is_float, const int64_t* index_dev, const void* buf_dev, int64_t n) {
+  if (!c) { set_error("null context"); return 1; }
+  if (n <= 0) return 0;
+  ANIB_CUDA_OK(cudaSetDevice(c->device));
+  unsigned g = (unsigned)((n * 3 + 255) / 256);
+  if (is_float) halo_unpack_add_kernel<float><<<g, 256, 0, c->stream>>>((float*)f_dev, index_dev, (const float*)buf_dev, n);
+  else halo_unpack_add_kernel<double><<<g, 256, 0, c->stream>>>((double*)f_dev, index_dev, (const double*)buf_dev, n);
+  ANIB_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,198 @@
+"""Python mirror of the reference's runner `class ANI` (src/ani_csrc/ani.h:11-84) over the C ABI.
+
+    ANI(model_file, local_rank, use_num_models=-1, use_cuaev=True, use_fullnbr=True, use_single=True)
+    .compute(species, coordinates, <neighbour data>, nlocal, ago, atomic, vflag)
+        -> (energy, force[ntotal,3], atomic_energies | None, virial[3,3] | None)     (kcal/mol, kcal/mol/A)
+
+Same argument meaning and error behaviour as the C++ class: neighbour data and species are only consumed when
+`ago == 0` (cached on the device otherwise, ani.cpp:122-137,213-229); a load failure raises RuntimeError
+(ani.cpp:93-96).  There is no CPU path: `local_rank == -1` ("cpu") raises.  The library is loaded with ctypes
+from lammps_ani_b200/libani_b200.so, and importing this module fails loudly if it has not been built.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import Optional
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libani_b200.so")
+HARTREE2KCALMOL = 627.5094738898777
+
+MLP_FP32_SIMT, MLP_TF32X3, MLP_TF32 = 0, 1, 2
+
+_lib = None
+
+
+def load_library():
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(f"{LIB_PATH} is missing: build it with `python -m lammps_ani_b200.build` "
+                           "(there is no Python/CPU fallback)")
+    L = C.CDLL(LIB_PATH)
+    vp, i32, i64, dp = C.c_void_p, C.c_int, C.c_int64, C.POINTER(C.c_double)
+    L.ani_last_error.restype = C.c_char_p
+    L.ani_abi_version.restype = i32
+    L.ani_model_load.argtypes = [C.c_char_p, C.POINTER(vp)]
+    L.ani_model_free.argtypes = [vp]
+    L.ani_model_info.argtypes = [vp, C.POINTER(i32), C.POINTER(i32), C.POINTER(i32), dp, dp]
+    L.ani_ctx_create.argtypes = [vp, i32, i32, i32, i32, i32, C.POINTER(vp)]
+    L.ani_ctx_destroy.argtypes = [vp]
+    L.ani_ctx_set_mlp_mode.argtypes = [vp, i32]
+    L.ani_ctx_set_stream.argtypes = [vp, vp]
+    L.ani_ctx_synchronize.argtypes = [vp]
+    L.ani_ctx_enable_timing.argtypes = [vp, i32]
+    L.ani_last_timing.argtypes = [vp, C.POINTER(C.c_float), C.POINTER(i32)]
+    L.ani_set_neighbors_full.argtypes = [vp, i32, i32, vp, i32, vp, vp, vp, i64, i32]
+    L.ani_set_neighbors_half.argtypes = [vp, i32, i32, vp, i64, vp, i32]
+    L.ani_compute.argtypes = [vp, vp, vp, vp, vp, vp]
+    L.ani_compute_device.argtypes = [vp, vp, i32, vp, i32, vp, vp, vp]
+    L.ani_debug_get_aev.argtypes = [vp, vp, vp]
+    L.ani_halo_pack_x.argtypes = [vp, vp, i32, vp, vp, i64, vp]
+    L.ani_halo_unpack_add_f.argtypes = [vp, vp, i32, vp, vp, i64]
+    for name in ("ani_model_load", "ani_model_info", "ani_ctx_create", "ani_ctx_set_mlp_mode", "ani_ctx_set_stream",
+                 "ani_ctx_synchronize", "ani_ctx_enable_timing", "ani_last_timing", "ani_set_neighbors_full",
+                 "ani_set_neighbors_half", "ani_compute", "ani_compute_device", "ani_debug_get_aev",
+                 "ani_halo_pack_x", "ani_halo_unpack_add_f"):
+        getattr(L, name).restype = i32
+    _lib = L
+    return L
+
+
+EXPORTED_SYMBOLS = [
+    "ani_model_load", "ani_model_free", "ani_model_info", "ani_ctx_create", "ani_ctx_destroy", "ani_ctx_set_mlp_mode",
+    "ani_ctx_set_stream", "ani_ctx_synchronize", "ani_set_neighbors_full", "ani_set_neighbors_half", "ani_compute",
+    "ani_compute_device", "ani_halo_pack_x", "ani_halo_unpack_add_f", "ani_debug_get_aev", "ani_last_timing",
+    "ani_ctx_enable_timing", "ani_last_error", "ani_abi_version",
+]
+
+
+def _check(rc: int):
+    if rc != 0:
+        raise RuntimeError("libani_b200: " + load_library().ani_last_error().decode())
+
+
+def _ptr(a):
+    return None if a is None else a.ctypes.data
+
+
+class ANI:
+    def __init__(self, model_file: str, local_rank: int, use_num_models: int = -1, use_cuaev: bool = True,
+                 use_fullnbr: bool = True, use_single: bool = True):
+        L = load_library()
+        self._L = L
+        self._model = C.c_void_p()
+        self._ctx = C.c_void_p()
+        _check(L.ani_model_load(os.fsencode(model_file), C.byref(self._model)))
+        ns, al, nm = C.c_int(), C.c_int(), C.c_int()
+        rcr, rca = C.c_double(), C.c_double()
+        _check(L.ani_model_info(self._model, C.byref(ns), C.byref(al), C.byref(nm), C.byref(rcr), C.byref(rca)))
+        self.num_species, self.aev_length, self.num_models = ns.value, al.value, nm.value
+        self.Rcr, self.Rca = rcr.value, rca.value
+        self.use_fullnbr, self.use_cuaev, self.use_single = use_fullnbr, use_cuaev, use_single
+        self.use_num_models = self.num_models if use_num_models == -1 else use_num_models
+        try:
+            _check(L.ani_ctx_create(self._model, local_rank, use_num_models, int(use_cuaev), int(use_fullnbr),
+                                    int(use_single), C.byref(self._ctx)))
+        except Exception:
+            L.ani_model_free(self._model)
+            self._model = C.c_void_p()
+            raise
+        self.nlocal = self.ntotal = 0
+
+    def close(self):
+        if getattr(self, "_ctx", None) and self._ctx:
+            self._L.ani_ctx_destroy(self._ctx)
+            self._ctx = C.c_void_p()
+        if getattr(self, "_model", None) and self._model:
+            self._L.ani_model_free(self._model)
+            self._model = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- knobs
+    def set_mlp_mode(self, mode: int):
+        _check(self._L.ani_ctx_set_mlp_mode(self._ctx, mode))
+
+    def set_stream(self, cuda_stream_ptr: Optional[int]):
+        _check(self._L.ani_ctx_set_stream(self._ctx, C.c_void_p(cuda_stream_ptr or 0)))
+
+    def synchronize(self):
+        _check(self._L.ani_ctx_synchronize(self._ctx))
+
+    def enable_timing(self, on: bool = True):
+        _check(self._L.ani_ctx_enable_timing(self._ctx, int(on)))
+
+    def last_timing(self):
+        ms = (C.c_float * 5)()
+        n = C.c_int()
+        _check(self._L.ani_last_timing(self._ctx, ms, C.byref(n)))
+        return list(ms), n.value
+
+    # ---- neighbour data (only when the list was rebuilt)
+    def set_neighbors_full(self, species, ilist, numneigh, jlist, nlocal: int):
+        species = np.ascontiguousarray(species, dtype=np.int32)
+        ilist = np.ascontiguousarray(ilist, dtype=np.int32)
+        numneigh = np.ascontiguousarray(numneigh, dtype=np.int32)
+        jlist = np.ascontiguousarray(jlist, dtype=np.int32)
+        self.nlocal, self.ntotal = int(nlocal), int(species.shape[0])
+        _check(self._L.ani_set_neighbors_full(self._ctx, self.nlocal, self.ntotal, _ptr(species), int(ilist.shape[0]),
+                                              _ptr(ilist), _ptr(numneigh), _ptr(jlist), int(jlist.shape[0]), 0))
+
+    def set_neighbors_half(self, species, atom_index12, nlocal: int):
+        species = np.ascontiguousarray(species, dtype=np.int32)
+        a = np.ascontiguousarray(atom_index12, dtype=np.int64).reshape(2, -1)
+        self.nlocal, self.ntotal = int(nlocal), int(species.shape[0])
+        _check(self._L.ani_set_neighbors_half(self._ctx, self.nlocal, self.ntotal, _ptr(species), int(a.shape[1]),
+                                              _ptr(a), 0))
+
+    # ---- one step, host arrays (ani.cpp:100-265)
+    def compute(self, species, coordinates, *nbr, nlocal: int, ago: int = 0, atomic: bool = False, vflag: bool = False):
+        if ago == 0:
+            if self.use_fullnbr:
+                ilist, jlist, numneigh = nbr      # argument order of the reference's full overload
+                self.set_neighbors_full(species, ilist, numneigh, jlist, nlocal)
+            else:
+                (atom_index12,) = nbr
+                self.set_neighbors_half(species, atom_index12, nlocal)
+        x = np.ascontiguousarray(coordinates, dtype=np.float64).reshape(-1, 3)
+        if x.shape[0] != self.ntotal:
+            raise ValueError("coordinates do not match the cached neighbour data (ago != 0 with a different system)")
+        energy = C.c_double()
+        force = np.empty((self.ntotal, 3), dtype=np.float64)
+        eatom = np.empty(self.nlocal, dtype=np.float64) if atomic else None
+        virial = np.empty(9, dtype=np.float64) if vflag else None
+        _check(self._L.ani_compute(self._ctx, _ptr(x), C.addressof(energy), _ptr(force), _ptr(eatom), _ptr(virial)))
+        return energy.value, force, eatom, (virial.reshape(3, 3) if vflag else None)
+
+    # ---- one step, device arrays (ani.cpp:268-316): raw CUDA pointers (e.g. torch.Tensor.data_ptr())
+    def compute_device(self, x_ptr: int, x_is_float: bool, f_ptr: int, f_is_float: bool, eatom_ptr: int = 0,
+                       want_energy: bool = True, want_virial: bool = False):
+        energy = C.c_double()
+        virial = np.empty(9, dtype=np.float64) if want_virial else None
+        _check(self._L.ani_compute_device(self._ctx, C.c_void_p(x_ptr), int(x_is_float), C.c_void_p(f_ptr),
+                                          int(f_is_float), C.c_void_p(eatom_ptr or 0),
+                                          C.addressof(energy) if want_energy else None, _ptr(virial)))
+        return (energy.value if want_energy else None), (virial.reshape(3, 3) if want_virial else None)
+
+    def halo_pack_x(self, x_ptr, is_float, index_ptr, shift_ptr, n, out_ptr):
+        _check(self._L.ani_halo_pack_x(self._ctx, C.c_void_p(x_ptr), int(is_float), C.c_void_p(index_ptr),
+                                       C.c_void_p(shift_ptr or 0), int(n), C.c_void_p(out_ptr)))
+
+    def halo_unpack_add_f(self, f_ptr, is_float, index_ptr, buf_ptr, n):
+        _check(self._L.ani_halo_unpack_add_f(self._ctx, C.c_void_p(f_ptr), int(is_float), C.c_void_p(index_ptr),
+                                             C.c_void_p(buf_ptr), int(n)))
+
+    def debug_aev(self, want_daev: bool = True):
+        aev = np.empty((self.nlocal, self.aev_length), dtype=np.float64)
+        daev = np.empty_like(aev) if want_daev else None
+        _check(self._L.ani_debug_get_aev(self._ctx, _ptr(aev), _ptr(daev)))
+        return aev, daev

@@ -123,7 +123,7 @@ def pyaev_forward(params, species, coordinates, atom_index12, nlocal, *, num_mod
     virial = dEdR.t() @ diff.detach()
     virial = -(virial.t() + virial) / 2
     k = HARTREE2KCALMOL
-    out = dict(energy=float(energy) * k, forces=(-dEdx).numpy() * k, eatom=eatom.detach().numpy() * k,
+    out = dict(energy=float(energy.detach()) * k, forces=(-dEdx).numpy() * k, eatom=eatom.detach().numpy() * k,
                virial=virial.numpy() * k)
     if want_aev:
         out["aev"] = aev.detach().numpy()[:nlocal]

@@ -1,0 +1,162 @@
+"""GPU parity tests (B200): the CUDA path through the C ABI against the CPU oracle on identical inputs.
+
+Tolerances are the north star's (BASELINE.json): fp32 total energy 1e-6 relative, per-atom forces 1e-4 eV/A
+max-abs (= 2.30605e-3 kcal/mol/A); `double` mode 1e-10 relative."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+from lammps_ani_b200 import domain
+from oracle.oracle import OracleANI
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+EV2KCAL = 23.060548
+F_TOL_FP32 = 1e-4 * EV2KCAL     # kcal/mol/A
+E_RTOL_FP32 = 1e-6
+RTOL_FP64 = 1e-10
+
+
+@pytest.fixture(scope="module")
+def ANI():
+    import torch
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    from lammps_ani_b200 import build, runner
+    build.build()
+    return runner.ANI
+
+
+def periodic_system(x, sp, box):
+    sub = domain.decompose(x, sp, np.asarray(box, dtype=float))[0]
+    il, nn, jl = domain.full_neighbor_list(sub.x, sub.nlocal)
+    return sub, il, nn, jl
+
+
+def check(gpu, ref, single, nlocal, f_scale=1.0):
+    e, f, eatom, virial = gpu
+    if single:
+        assert abs(e - ref["energy"]) <= E_RTOL_FP32 * abs(ref["energy"])
+        assert np.abs(f - ref["forces"]).max() <= F_TOL_FP32 * f_scale
+        if eatom is not None:
+            assert np.abs(eatom - ref["eatom"]).max() <= 1e-5 * np.abs(ref["eatom"]).max()
+        if virial is not None:
+            assert np.abs(virial - ref["virial"]).max() <= 2e-5 * max(1.0, np.abs(ref["virial"]).max())
+    else:
+        assert abs(e - ref["energy"]) <= RTOL_FP64 * abs(ref["energy"])
+        assert np.abs(f - ref["forces"]).max() <= RTOL_FP64 * max(1.0, np.abs(ref["forces"]).max())
+        if eatom is not None:
+            assert np.abs(eatom - ref["eatom"]).max() <= RTOL_FP64 * np.abs(ref["eatom"]).max()
+        if virial is not None:
+            assert np.abs(virial - ref["virial"]).max() <= RTOL_FP64 * max(1.0, np.abs(ref["virial"]).max())
+
+
+@pytest.mark.parametrize("single", [False, True])
+def test_water30_reference_half_list(ANI, water30, ani1xnr_path, single):
+    """The reference's own known-answer input (test_model.cpp:84-120): non-periodic, half list, all members."""
+    orc = OracleANI(ani1xnr_path)
+    ref = orc.compute_half(water30["species"], water30["x"], water30["atom_index12"], 30, single_coords=single)
+    ani = ANI(ani1xnr_path, 0, -1, use_cuaev=True, use_fullnbr=False, use_single=single)
+    out = ani.compute(water30["species"], water30["x"], water30["atom_index12"], nlocal=30, ago=0, atomic=True, vflag=True)
+    check(out, ref, single, 30)
+    with open(os.path.join(ROOT, "tests", "golden", "water30_ani1xnr.json")) as f:
+        g = json.load(f)["cases"][0]
+    tol = E_RTOL_FP32 if single else RTOL_FP64
+    assert abs(out[0] - g["energy"]) <= tol * abs(g["energy"])
+    assert np.abs(out[1] - np.array(g["forces"])).max() <= (F_TOL_FP32 if single else 1e-8)
+
+
+@pytest.mark.parametrize("single", [False, True])
+@pytest.mark.parametrize("model", ["ani1xnr", "ani2x_synth"])
+def test_water30_periodic_full_list_with_ghosts(ANI, water30, ani1xnr_path, ani2x_synth_path, single, model):
+    path = ani1xnr_path if model == "ani1xnr" else ani2x_synth_path
+    sub, il, nn, jl = periodic_system(water30["x"] + 4.0, water30["species"], [8.0, 8.0, 8.0])
+    ref = OracleANI(path).compute_full(sub.species, sub.x, il, nn, jl, sub.nlocal, single_coords=single, want_aev=True,
+                                       want_daev=True)
+    ani = ANI(path, 0, -1, True, True, single)
+    out = ani.compute(sub.species, sub.x, il, jl, nn, nlocal=sub.nlocal, ago=0, atomic=True, vflag=True)
+    aev, daev = ani.debug_aev()
+    if single:
+        assert np.abs(aev - ref["aev"]).max() <= 2e-5 * max(1.0, np.abs(ref["aev"]).max())
+        assert np.abs(daev - ref["daev"]).max() <= 2e-5 * max(1.0, np.abs(ref["daev"]).max())
+    else:
+        assert np.abs(aev - ref["aev"]).max() <= 1e-12 * max(1.0, np.abs(ref["aev"]).max())
+        assert np.abs(daev - ref["daev"]).max() <= 1e-11 * max(1.0, np.abs(ref["daev"]).max())
+    check(out, ref, single, sub.nlocal)
+    # ago != 0: cached neighbour data, slightly moved coordinates (ani.cpp:213-229 semantics)
+    x2 = sub.x + 1e-3 * np.sin(np.arange(sub.x.size).reshape(sub.x.shape))
+    # ghosts must move with their owners
+    x2[sub.nlocal:] = sub.x[sub.nlocal:] + (x2[sub.ghost_owner_index] - sub.x[sub.ghost_owner_index])
+    ref2 = OracleANI(path).compute_full(sub.species, x2, il, nn, jl, sub.nlocal, single_coords=single)
+    out2 = ani.compute(None, x2, nlocal=sub.nlocal, ago=1, atomic=True, vflag=True)
+    check(out2, ref2, single, sub.nlocal)
+
+
+@pytest.mark.parametrize("single", [False, True])
+def test_water_box_2k_atoms(ANI, ani2x_synth_path, single):
+    """ANI-2x geometry, all 8 members, 2 160-atom periodic water box (8x9x10 molecules)."""
+    x, sp, box = domain.make_water_box((8, 9, 10), seed=7)
+    sub, il, nn, jl = periodic_system(x, sp, box)
+    ref = OracleANI(ani2x_synth_path).compute_full(sub.species, sub.x, il, nn, jl, sub.nlocal, single_coords=single)
+    ani = ANI(ani2x_synth_path, 0, -1, True, True, single)
+    out = ani.compute(sub.species, sub.x, il, jl, nn, nlocal=sub.nlocal, ago=0, atomic=True, vflag=True)
+    check(out, ref, single, sub.nlocal)
+    # folded forces sum to zero (translation invariance) -- a size-independent property
+    f = domain.fold_ghost_forces(sub, out[1])
+    assert np.abs(f.sum(0)).max() < (2e-2 if single else 1e-7)
+
+
+def test_half_equals_full_and_num_models(ANI, ani1xnr_path):
+    x, sp, box = domain.make_water_box((4, 4, 4), seed=3)
+    sub, il, nn, jl = periodic_system(x, sp, box)
+    half = domain.half_neighbor_list(sub.x, sub.nlocal)
+    full = ANI(ani1xnr_path, 0, 4, True, True, False).compute(sub.species, sub.x, il, jl, nn, nlocal=sub.nlocal, vflag=True)
+    hal = ANI(ani1xnr_path, 0, 4, True, False, False).compute(sub.species, sub.x, half, nlocal=sub.nlocal, vflag=True)
+    assert abs(full[0] - hal[0]) < 1e-10 * abs(full[0])
+    assert np.abs(full[1] - hal[1]).max() < 1e-8
+    ref = OracleANI(ani1xnr_path, use_num_models=4).compute_full(sub.species, sub.x, il, nn, jl, sub.nlocal)
+    check(full, ref, False, sub.nlocal)
+    allm = ANI(ani1xnr_path, 0, -1, True, True, False).compute(sub.species, sub.x, il, jl, nn, nlocal=sub.nlocal)
+    assert abs(allm[0] - full[0]) > 1e-6
+
+
+def test_pyaev_mode_has_no_radial_refilter(ANI, ani1xnr_path, water30):
+    """use_cuaev=False reproduces the behaviour the reference's pyaev goldens encode."""
+    x, sp = water30["x"], water30["species"]
+    ref = OracleANI(ani1xnr_path).compute_half(sp, x, water30["atom_index12"], 30, radial_filter=False)
+    out = ANI(ani1xnr_path, 0, -1, False, False, False).compute(sp, x, water30["atom_index12"], nlocal=30, vflag=True)
+    check(out, ref, False, 30)
+
+
+def test_mixed_species_buckets(ANI, ani2x_synth_path):
+    """All 7 ANI-2x species present, some buckets tiny or empty-then-filled (alanine-dipeptide-like mix)."""
+    rng = np.random.default_rng(5)
+    x, sp, box = domain.make_water_box((5, 5, 5), seed=11)
+    sp = sp.copy()
+    pick = rng.choice(len(sp), size=40, replace=False)
+    sp[pick] = rng.integers(0, 7, size=40)
+    sub, il, nn, jl = periodic_system(x, sp, box)
+    for single in (False, True):
+        ref = OracleANI(ani2x_synth_path).compute_full(sub.species, sub.x, il, nn, jl, sub.nlocal, single_coords=single)
+        out = ANI(ani2x_synth_path, 0, -1, True, True, single).compute(sub.species, sub.x, il, jl, nn, nlocal=sub.nlocal,
+                                                                      atomic=True, vflag=True)
+        check(out, ref, single, sub.nlocal)
+
+
+def test_error_paths(ANI, ani1xnr_path, water30):
+    ani = ANI(ani1xnr_path, 0)
+    sp = water30["species"].copy()
+    sp[3] = 6     # species outside the 4-species model
+    il, nn, jl = domain.full_neighbor_list(water30["x"], 30)
+    with pytest.raises(RuntimeError):
+        ani.compute(sp, water30["x"], il, jl, nn, nlocal=30)
+    with pytest.raises(RuntimeError):
+        ANI(ani1xnr_path, 0, 9)        # more members than the ensemble has
+    with pytest.raises(RuntimeError):
+        ANI(ani1xnr_path, -1)          # "cpu"
+    # empty system
+    e, f, _, _ = ani.compute(np.zeros(0, dtype=np.int32), np.zeros((0, 3)), np.zeros(0, np.int32), np.zeros(0, np.int32),
+                             np.zeros(0, np.int32), nlocal=0)
+    assert e == 0.0 and f.shape == (0, 3)
