@@ -1,0 +1,335 @@
+#!/usr/bin/env python
+"""bench.py -- ANI-2x water atom-timesteps/s on N B200 (BASELINE.json metric), one process per GPU.
+
+    python bench.py --gpus 1 --steps 20 --warmup 5
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P \
+        bench.py --gpus N --steps K --warmup W
+    python bench.py --impl reference ...      # CPU arm: the oracle port on the host cores
+
+Workload (config.workload): the reference's `examples/water` case -- a ~300 k-atom periodic water box per GPU,
+ANI-2x geometry (7 species, 1008-long AEV), all 8 ensemble members, fp32, full neighbour list at 5.1+2.0 A --
+weak-scaled the way the reference does it (`replicate`: one identical replica per rank, brick grid 1x1x1 /
+2x1x1 / 2x2x1 / 2x2x2).  ANI-2x weights are not available offline: seeded random weights of the ANI-2x shapes
+(throughput does not depend on the values).  A step = forward halo (ghost positions) -> AEV -> ensemble MLP
+fwd+bwd -> force/virial scatter -> reverse halo (ghost forces); coordinates are static, the neighbour list is
+uploaded once (LAMMPS re-uploads it every ~10 steps; that rebuild is outside this path).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+A100_PUBLISHED_M8 = 1.125e6   # 300 k water, Kokkos, 8 models, 1xA100 (examples/water/README.md:29-32)
+DT_FS = 0.5
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--atoms", type=int, default=int(os.environ.get("ANI_BENCH_ATOMS", 300000)), help="atoms per GPU")
+    ap.add_argument("--models", type=int, default=8)
+    ap.add_argument("--mlp-mode", default=os.environ.get("ANI_B200_MLP_MODE", ""), help="simt | tf32x3 | tf32")
+    ap.add_argument("--cpu-sample-atoms", type=int, default=0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+def model_path(num_models_total=8):
+    from lammps_ani_b200 import aniw, extract
+    d = os.path.join(ROOT, "lammps_ani_b200", "data")
+    os.makedirs(d, exist_ok=True)
+    p = os.path.join(d, "ani2x_synthetic_seed2024.aniw")
+    if not os.path.exists(p):
+        tmp = p + f".tmp{os.getpid()}"
+        aniw.save(extract.synthetic_ani2x(seed=2024, num_models=num_models_total), tmp)
+        os.replace(tmp, p)
+    return p
+
+
+def build_system(atoms_per_gpu, grid, rank):
+    from lammps_ani_b200 import domain
+    cells = domain.cells_for_atoms(atoms_per_gpu)
+    x, sp, box = domain.make_water_box(cells, seed=12345)
+    sub = domain.decompose(x, sp, box, (1, 1, 1))[0]
+    halo = domain.replica_halo(sub, box, grid, rank)
+    il, nn, jl = domain.full_neighbor_list(sub.x, sub.nlocal)
+    return cells, box, sub, halo, il, nn, jl
+
+
+def flops_per_step(params, species_local, M):
+    counts = np.bincount(species_local, minlength=params.num_species)
+    macs = sum(int(counts[s]) * params.macs_per_atom(s) for s in range(params.num_species))
+    return 4.0 * M * macs          # fwd 2*MACs + dE/dAEV backward 2*MACs per member
+
+
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons, pw = [], [], set(), []
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for l in self.lines:
+            parts = [p.strip() for p in l.split(",")]
+            if len(parts) < 7:
+                continue
+            try:
+                sm.append(float(parts[0])); mx.append(float(parts[1])); pw.append(float(parts[2]))
+            except ValueError:
+                continue
+            for n, v in zip(names, parts[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def cpu_baseline(model, sub, il, nn, jl, M, sample_atoms, repeats=1):
+    """Oracle port (oracle/ani_oracle.c, OpenMP over centres) on the first `sample_atoms` local atoms."""
+    from oracle.oracle import OracleANI
+    ncores = os.cpu_count() or 1
+    orc = OracleANI(model, use_num_models=M, nthreads=ncores)
+    S = min(sample_atoms, sub.nlocal)
+    off = np.concatenate([[0], np.cumsum(nn[:S].astype(np.int64))])
+    nbr = jl[:off[-1]]
+    best = None
+    for _ in range(repeats):
+        t0 = time.perf_counter()
+        orc.compute_csr(sub.species, sub.x, S, off, nbr)
+        dt = time.perf_counter() - t0
+        best = dt if best is None else min(best, dt)
+    return S / best, S, ncores, best
+
+
+def run_reference(args):
+    """CPU arm: times the oracle port on all host threads, same workload/metric; rank 0 only."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    from lammps_ani_b200 import aniw
+    model = model_path()
+    cells, box, sub, halo, il, nn, jl = build_system(min(args.atoms, 40000), (1, 1, 1), 0)
+    # size the per-step sample for ~3 s of CPU work
+    rate, S0, ncores, dt = cpu_baseline(model, sub, il, nn, jl, args.models, 256)
+    S = args.cpu_sample_atoms or int(max(256, min(sub.nlocal, rate * 3.0)))
+    for _ in range(args.warmup):
+        cpu_baseline(model, sub, il, nn, jl, args.models, S)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        cpu_baseline(model, sub, il, nn, jl, args.models, S)
+    total = time.perf_counter() - t0
+    value = S * args.steps / total
+    line = {
+        "impl": "reference", "metric": "ANI-2x water atom-timesteps/s", "value": value, "unit": "atom-timesteps/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": f"water box, ANI-2x geometry, {args.models} members, full list 7.1 A; CPU arm evaluates a "
+                               f"{S}-atom sample of the box per step", "atoms_per_gpu": args.atoms},
+        "cpu_baseline": {"value": value, "unit": "atom-timesteps/s", "cores": ncores, "kind": "port",
+                         "sample": f"{S} centre atoms (with their full neighbour shells) of the water box per step, "
+                                   f"{args.steps} steps; oracle/ani_oracle.c with OpenMP on {ncores} threads"},
+        "e2e": {"value": value, "unit": "atom-timesteps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "ns_per_day_300k": value / 300000 * DT_FS * 86400e-6,
+    }
+    print(json.dumps(line))
+    return 0
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+    import torch
+    import torch.distributed as dist
+    if not torch.cuda.is_available():
+        print("bench.py: no CUDA device (the product path has no CPU fallback)", file=sys.stderr)
+        return 2
+    from lammps_ani_b200 import aniw, build, domain, runner
+    from lammps_ani_b200.ddstep import GpuDomainStep
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        if world == 1 and args.gpus > 1:
+            print(f"bench.py: --gpus {args.gpus} needs torchrun with {args.gpus} ranks", file=sys.stderr)
+            return 2
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    if rank == 0:
+        build.build()
+        model_path()
+    if world > 1:
+        dist.barrier()
+    model = model_path()
+    params = aniw.load(model)
+    grid = domain.grid_for_ranks(world)
+    t_setup = time.time()
+    cells, box, sub, halo, il, nn, jl = build_system(args.atoms, grid, rank)
+    M = args.models
+    ani = runner.ANI(model, local_rank, M, use_cuaev=True, use_fullnbr=True, use_single=True)
+    mode_names = {"simt": runner.MLP_FP32_SIMT, "tf32x3": runner.MLP_TF32X3, "tf32": runner.MLP_TF32}
+    if args.mlp_mode:
+        ani.set_mlp_mode(mode_names[args.mlp_mode])
+    step = GpuDomainStep(ani, sub, halo, dev, il, nn, jl)
+    t_setup = time.time() - t_setup
+    nlocal, ntotal = sub.nlocal, sub.ntotal
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---------------- device-resident timed region (value)
+    for _ in range(max(args.warmup, 3)):
+        step.step_gpu()
+    barrier()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for _ in range(args.steps):
+        step.step_gpu()
+    e1.record()
+    barrier()
+    ms = e0.elapsed_time(e1)
+    _, launches = ani.last_timing()
+    launches += 2   # halo pack + unpack kernels
+    # ---------------- end-to-end: host buffers in / out every step
+    x_host = torch.from_numpy(np.ascontiguousarray(sub.x[:nlocal])).pin_memory()
+    f_host = torch.empty((nlocal, 3), dtype=torch.float64).pin_memory()
+    for _ in range(2):
+        step.x[:nlocal].copy_(x_host, non_blocking=True); step.step_gpu(True); f_host.copy_(step.f[:nlocal], non_blocking=True)
+    barrier()
+    g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    g0.record()
+    for _ in range(args.steps):
+        step.x[:nlocal].copy_(x_host, non_blocking=True)
+        energy = step.step_gpu(want_energy=True)          # reads the energy back (stream sync)
+        f_host.copy_(step.f[:nlocal], non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+    g1.record()
+    barrier()
+    ms_e2e = g0.elapsed_time(g1)
+    clocks = sampler.stop()
+    # ---------------- per-stage device times (library CUDA events on the same stream), a few extra steps
+    ani.enable_timing(True)
+    stage = np.zeros(5)
+    nst = 5
+    for _ in range(nst):
+        step.step_gpu(True)
+        t, _n = ani.last_timing()
+        stage += np.array(t)
+    stage /= nst
+    ani.enable_timing(False)
+    # ---------------- reduce over ranks (max time)
+    tm = torch.tensor([ms, ms_e2e], dtype=torch.float64, device=dev)
+    cnt = torch.tensor([float(nlocal)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(tm, op=dist.ReduceOp.MAX)
+        dist.all_reduce(cnt, op=dist.ReduceOp.SUM)
+    ms, ms_e2e = float(tm[0]), float(tm[1])
+    natoms_total = float(cnt[0])
+    value = natoms_total * args.steps / (ms * 1e-3)
+    value_e2e = natoms_total * args.steps / (ms_e2e * 1e-3)
+
+    if rank == 0:
+        peaks = {}
+        pk = os.path.join(ROOT, "MEASURED_PEAKS.json")
+        if os.path.exists(pk):
+            peaks = json.load(open(pk))
+        hbm = peaks.get("hbm_gbs", 6650.0)
+        bf16 = peaks.get("bf16_tflops_sustained", 1400.0)
+        which = "MEASURED_PEAKS.json" if peaks else "fallback (B200_PROFILING.md)"
+        fl = flops_per_step(params, sub.species[:nlocal], M)
+        mlp_ms = max(stage[2], 1e-9)
+        mode = {0: "fp32 FFMA (SIMT)", 1: "tcgen05 tf32x3", 2: "tcgen05 tf32"}.get(
+            mode_names.get(args.mlp_mode, 0), "?")
+        tf32_peak = bf16 / 2.0
+        ach = fl / (mlp_ms * 1e-3) / 1e12
+        L = params.aev_length
+        aev_bytes = nlocal * (4.0 * float(jl.size) / nlocal + 8 + 16 + 4 * L)       # list + x + AEV row store
+        bwd_bytes = nlocal * (4.0 * L + 4.0 * float(jl.size) / nlocal + 16 + 12)
+        roofline = {"kernel": f"ensemble MLP fwd+bwd GEMM stage ({mode})", "bound": "tensor", "achieved": ach,
+                    "peak": tf32_peak, "unit": "TFLOP/s", "frac": ach / tf32_peak, "traffic": None,
+                    "peak_source": f"{which}: bf16_tflops_sustained/2 taken as the dense TF32 peak",
+                    "algorithmic_flops_per_step": fl, "ms": mlp_ms}
+        stages = {"pack_ms": stage[0], "aev_fwd_ms": stage[1], "mlp_ms": stage[2], "aev_bwd_ms": stage[3], "reduce_d2h_ms": stage[4],
+                  "aev_fwd_GBps": aev_bytes / (max(stage[1], 1e-9) * 1e-3) / 1e9, "aev_bwd_GBps": bwd_bytes / (max(stage[3], 1e-9) * 1e-3) / 1e9,
+                  "hbm_peak_GBps": hbm}
+        line = {
+            "metric": "ANI-2x water atom-timesteps/s", "value": value, "unit": "atom-timesteps/s", "n_gpus": world,
+            "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": value / A100_PUBLISHED_M8 if (M == 8) else None, "dtype": "f32",
+            "data": "synthetic",
+            "config": {"workload": f"examples/water-style periodic water box, {nlocal} atoms + {ntotal - nlocal} ghosts per GPU "
+                                   f"(lattice {cells[0]}x{cells[1]}x{cells[2]} molecules), ANI-2x geometry (1008 AEV, 7 species), "
+                                   f"{M} ensemble members, fp32, full neighbour list 7.1 A ({jl.size / nlocal:.1f}/atom), "
+                                   f"replicate grid {grid[0]}x{grid[1]}x{grid[2]}",
+                       "weights": "seeded random, ANI-2x shapes (real ANI-2x parameters unavailable offline)",
+                       "mlp_mode": mode, "l2": "inputs larger than L2 (AEV rows alone exceed 126 MB); no explicit flush",
+                       "vs_baseline_note": "published number is 1xA100, Kokkos, 300k water, 8 models (BASELINE.md)",
+                       "setup_s": t_setup},
+            "ns_per_day": (args.steps / (ms * 1e-3)) * DT_FS * 86400e-6,
+            "e2e": {"value": value_e2e, "unit": "atom-timesteps/s", "h2d_bytes_per_step": int(nlocal * 24 * world),
+                    "d2h_bytes_per_step": int((nlocal * 24 + 8) * world), "ms_per_step": ms_e2e / args.steps,
+                    "path": "pinned host x[nlocal] -> device, halo + ani_compute_device + halo, device f[nlocal] + energy -> host"},
+            "gpu_launches": int(launches) * args.steps, "gpu_launches_per_step": int(launches),
+            "clocks": clocks, "roofline": roofline, "stages": stages,
+        }
+        if not args.no_cpu_baseline and world == 1:
+            rate, S0, ncores, dt = cpu_baseline(model, sub, il, nn, jl, M, 256)
+            S = args.cpu_sample_atoms or int(max(256, min(nlocal, rate * 12.0)))
+            rate, S, ncores, dt = cpu_baseline(model, sub, il, nn, jl, M, S)
+            line["cpu_baseline"] = {"value": rate, "unit": "atom-timesteps/s", "cores": ncores, "kind": "port",
+                                    "sample": f"{S} centre atoms of the same box, one pass ({dt:.1f} s), oracle/ani_oracle.c OpenMP fp64"}
+        print(json.dumps(line))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -73,6 +73,7 @@ class Subdomain:
     species: np.ndarray           # [ntotal] int32 (type-1)
     ghost_owner_rank: np.ndarray  # [nghost] rank owning the real atom
     ghost_owner_index: np.ndarray  # [nghost] local index on the owner
+    ghost_shift: np.ndarray       # [nghost,3] periodic image shift (in box lengths) that produced the ghost
     global_id: np.ndarray         # [ntotal] id in the global box
     lo: np.ndarray
     hi: np.ndarray
@@ -89,7 +90,7 @@ class Subdomain:
 def _ghost_images(pos, box, lo, hi, cut, periodic=True):
     """All images (including shift 0 for atoms outside [lo,hi)) of `pos` inside the halo shell of the brick
     [lo-cut, hi+cut) minus the brick itself.  Returns (index into pos, shifted coordinates)."""
-    idx_all, x_all = [], []
+    idx_all, x_all, s_all = [], [], []
     rng = [-1, 0, 1] if periodic else [0]
     # enough images when box >= cut; for tiny boxes (8 A box, 7.1 A halo) allow +-ceil(cut/box) images
     reach = [int(np.ceil(cut / b)) if periodic else 0 for b in box]
@@ -104,9 +105,10 @@ def _ghost_images(pos, box, lo, hi, cut, periodic=True):
                 if sel.size:
                     idx_all.append(sel)
                     x_all.append(y[sel])
+                    s_all.append(np.tile(np.array([sx, sy, sz], dtype=np.int64), (sel.size, 1)))
     if not idx_all:
-        return np.zeros(0, dtype=np.int64), np.zeros((0, 3))
-    return np.concatenate(idx_all), np.concatenate(x_all)
+        return np.zeros(0, dtype=np.int64), np.zeros((0, 3)), np.zeros((0, 3), dtype=np.int64)
+    return np.concatenate(idx_all), np.concatenate(x_all), np.concatenate(s_all)
 
 
 def decompose(pos, species, box, grid=(1, 1, 1), cut: float = LIST_CUTOFF, periodic: bool = True) -> List[Subdomain]:
@@ -129,11 +131,12 @@ def decompose(pos, species, box, grid=(1, 1, 1), cut: float = LIST_CUTOFF, perio
         lo = np.array([ix, iy, iz]) * cell
         hi = lo + cell
         ids = local_ids[r]
-        gidx, gx = _ghost_images(pos, box, lo, hi, cut, periodic)
+        gidx, gx, gshift = _ghost_images(pos, box, lo, hi, cut, periodic)
         x = np.concatenate([pos[ids], gx])
         sp = np.concatenate([species[ids], species[gidx]]).astype(np.int32)
         out.append(Subdomain(nlocal=ids.size, x=x, species=sp, ghost_owner_rank=owner_rank[gidx],
-                             ghost_owner_index=local_index[gidx], global_id=np.concatenate([ids, gidx]),
+                             ghost_owner_index=local_index[gidx], ghost_shift=gshift,
+                             global_id=np.concatenate([ids, gidx]),
                              lo=lo, hi=hi))
     return out
 
@@ -198,6 +201,7 @@ def halo_plans(subs: List[Subdomain], pos_global: np.ndarray) -> List[HaloPlan]:
         s.global_id[nl:] = s.global_id[nl:][order]
         s.ghost_owner_rank = s.ghost_owner_rank[order]
         s.ghost_owner_index = s.ghost_owner_index[order]
+        s.ghost_shift = s.ghost_shift[order]
     plans = [HaloPlan([None] * n, [None] * n, [0] * n, [0] * n) for _ in range(n)]
     for r, s in enumerate(subs):
         counts = np.bincount(s.ghost_owner_rank, minlength=n)
@@ -211,3 +215,83 @@ def halo_plans(subs: List[Subdomain], pos_global: np.ndarray) -> List[HaloPlan]:
             plans[o].send_index[r] = oi.astype(np.int64)
             plans[o].send_shift[r] = shift
     return plans
+
+
+# ----------------------------------------------------------------------------------------------------------
+# Weak scaling the way the reference does it: LAMMPS `replicate px py pz` of one periodic base box
+# (/root/reference/examples/benchmark/in.lammps:31, submit_scaling.py:13-22), one replica per rank.  Every rank
+# then holds the SAME local box; only the owners of its ghosts differ (the neighbour replica in direction s).
+
+DIRECTIONS = [(sx, sy, sz) for sx in (-1, 0, 1) for sy in (-1, 0, 1) for sz in (-1, 0, 1) if (sx, sy, sz) != (0, 0, 0)]
+
+
+def grid_for_ranks(n: int) -> Tuple[int, int, int]:
+    """1 -> 1x1x1, 2 -> 2x1x1, 4 -> 2x2x1, 8 -> 2x2x2 (submit_scaling.py:13-22); other counts: near-cubic factors."""
+    table = {1: (1, 1, 1), 2: (2, 1, 1), 4: (2, 2, 1), 8: (2, 2, 2)}
+    if n in table:
+        return table[n]
+    g = [1, 1, 1]
+    k, f = n, 2
+    while k > 1:
+        while k % f == 0:
+            g[int(np.argmin(g))] *= f
+            k //= f
+        f += 1
+    return tuple(sorted(g, reverse=True))
+
+
+def rank_coords(rank: int, grid) -> Tuple[int, int, int]:
+    ix, rem = divmod(rank, grid[1] * grid[2])
+    iy, iz = divmod(rem, grid[2])
+    return ix, iy, iz
+
+
+def coords_rank(q, grid) -> int:
+    return ((q[0] % grid[0]) * grid[1] + (q[1] % grid[1])) * grid[2] + (q[2] % grid[2])
+
+
+@dataclass
+class ReplicaHalo:
+    """Halo exchange description of one rank in a replicated run.  Ghost atoms are re-ordered so that the block
+    received from each source rank is contiguous; `send_index`/`send_shift` are already concatenated in
+    destination-rank order, ready for one all_to_all_single."""
+    send_index: np.ndarray        # [nsend] local atom index
+    send_shift: np.ndarray        # [nsend,3] displacement to add (receiver's frame), Angstrom
+    send_splits: List[int]        # per destination rank
+    recv_splits: List[int]        # per source rank (sum == nghost)
+
+
+def replica_halo(sub: Subdomain, box, grid, rank: int) -> ReplicaHalo:
+    """Re-orders sub's ghosts in place (x, species, owner index, shift) and returns the exchange plan."""
+    n = int(np.prod(grid))
+    q = rank_coords(rank, grid)
+    if np.abs(sub.ghost_shift).max(initial=0) > 1:
+        raise ValueError("replicated runs need a base box at least as wide as the halo")
+    dir_id = {d: k for k, d in enumerate(DIRECTIONS)}
+    gdir = np.array([dir_id[tuple(s)] for s in sub.ghost_shift], dtype=np.int64) if sub.nghost else np.zeros(0, np.int64)
+    src_of_dir = np.array([coords_rank((q[0] + d[0], q[1] + d[1], q[2] + d[2]), grid) for d in DIRECTIONS])
+    dst_of_dir = np.array([coords_rank((q[0] - d[0], q[1] - d[1], q[2] - d[2]), grid) for d in DIRECTIONS])
+    gsrc = src_of_dir[gdir] if sub.nghost else np.zeros(0, np.int64)
+    order = np.lexsort((np.arange(sub.nghost), gdir, gsrc))      # by source rank, then direction, stable
+    nl = sub.nlocal
+    sub.x[nl:] = sub.x[nl:][order]
+    sub.species[nl:] = sub.species[nl:][order]
+    sub.global_id[nl:] = sub.global_id[nl:][order]
+    sub.ghost_owner_index = sub.ghost_owner_index[order]
+    sub.ghost_shift = sub.ghost_shift[order]
+    sub.ghost_owner_rank = gsrc[order]
+    gdir = gdir[order]
+    recv_splits = np.bincount(sub.ghost_owner_rank, minlength=n).astype(int).tolist()
+    # what I send "with shift d" is what I myself receive with shift d (identical replicas), to rank q - d
+    send_idx, send_shift, send_dst = [], [], []
+    for k, d in enumerate(DIRECTIONS):
+        sel = np.nonzero(gdir == k)[0]
+        send_idx.append(sub.ghost_owner_index[sel])
+        send_shift.append(np.tile(np.array(d, dtype=np.float64) * np.asarray(box), (sel.size, 1)))
+        send_dst.append(np.full(sel.size, dst_of_dir[k]))
+    send_idx = np.concatenate(send_idx) if send_idx else np.zeros(0, np.int64)
+    send_shift = np.concatenate(send_shift) if send_shift else np.zeros((0, 3))
+    send_dst = np.concatenate(send_dst) if send_dst else np.zeros(0, np.int64)
+    sorder = np.argsort(send_dst, kind="stable")                 # by destination rank, direction order preserved
+    return ReplicaHalo(send_index=send_idx[sorder].astype(np.int64), send_shift=send_shift[sorder],
+                       send_splits=np.bincount(send_dst, minlength=n).astype(int).tolist(), recv_splits=recv_splits)
