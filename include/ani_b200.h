@@ -101,6 +101,10 @@ int ani_debug_get_aev(ani_ctx* ctx, double* out_aev, double* out_daev);
 int ani_last_timing(ani_ctx* ctx, float stage_ms[5], int* num_launches);
 int ani_ctx_enable_timing(ani_ctx* ctx, int on);
 
+/* Test hook for the tensor-core GEMM kernel alone: C[R][N] = A[R][K] . B[N][K]^T (host pointers, row major),
+ * three_pass = 1: TF32x3 split, 0: single TF32.  N must have a divisor <= 256 that is a multiple of 16; K % 8 == 0. */
+int ani_debug_tc_gemm(int device, int R, int N, int K, const float* A, const float* B, float* C, int three_pass);
+
 const char* ani_last_error(void);
 int ani_abi_version(void);
 

@@ -485,7 +485,7 @@ template <> int Engine<double>::mlp_tc_species(int, int, int) {
 
 template <> int Engine<float>::mlp_tc_species(int s, int row0, int R) {
   return tc_mlp_species(c->stream, c->mlp_mode == ANI_MLP_TF32X3, nets[s].tc, tcw, M, nets[s].dims, d_aev_hi.as<float>(),
-                        d_aev_lo.as<float>(), ld_aev, row0, R, d_daev.as<float>(), d_eatom.as<double>(), hm.sae[s],
+                        d_aev_lo.as<float>(), ld_aev, nlocal, row0, R, d_daev.as<float>(), d_eatom.as<double>(), hm.sae[s],
                         &c->launches);
 }
 
@@ -548,7 +548,7 @@ int ani_ctx_create(const ani_model* model, int device, int use_num_models, int u
     auto* e = new Engine<float>(c.get(), model->hm, M);
     c->eng.reset(e);
     rc = e->init();
-    if (!rc) rc = tc_prepare_weights(model->hm, M, e->nets);
+    for (int s = 0; s < model->hm.S && !rc; s++) rc = tc_prepare_species(model->hm, M, s, e->nets[s].tc);
   } else {
     auto* e = new Engine<double>(c.get(), model->hm, M);
     c->eng.reset(e);
@@ -698,6 +698,29 @@ int ani_debug_get_aev(ani_ctx* c, double* aev, double* daev) {
   if (!c) { set_error("null context"); return 1; }
   ANIB_CUDA_OK(cudaSetDevice(c->device));
   return c->eng->get_aev(aev, daev);
+}
+
+int ani_debug_tc_gemm(int device, int R, int N, int K, const float* A, const float* B, float* C, int three_pass) {
+  using namespace anib::tc;
+  if (!A || !B || !C || R < 1 || N < 16 || K < 8 || K % 8 != 0 || pick_bn(N) == 0) { set_error("ani_debug_tc_gemm: bad arguments"); return 1; }
+  ANIB_CUDA_OK(cudaSetDevice(device));
+  DevBufTc a_hi, a_lo, b_hi, b_lo, c_d;
+  std::vector<float> av(A, A + (size_t)R * K), bv(B, B + (size_t)N * K);
+  if (upload_planes(av, a_hi, a_lo) || upload_planes(bv, b_hi, b_lo)) return 1;
+  if (!c_d.reserve((size_t)R * N * 4)) { set_error("out of memory"); return 1; }
+  int num_sms = 0, max_smem = 0;
+  cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, device);
+  cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, device);
+  Launcher L{nullptr, num_sms, nullptr, max_smem};
+  GemmArgs g{};
+  g.BN = pick_bn(N); g.R = R; g.N = N; g.num_n_tiles = N / g.BN; g.num_row_tiles = (R + BM - 1) / BM; g.K = K; g.batch = 1;
+  g.three_pass = three_pass ? 1 : 0; g.out_hi = c_d.f(); g.ld_out = N; g.scale = 1.0f;
+  if (launch_gemm<EPI_D>(L, a_hi.f(), a_lo.f(), (uint64_t)R, (uint64_t)K, (uint64_t)K, b_hi.f(), b_lo.f(), (uint64_t)N, (uint64_t)K,
+                         (uint64_t)K, g))
+    return 1;
+  ANIB_CUDA_OK(cudaDeviceSynchronize());
+  ANIB_CUDA_OK(cudaMemcpy(C, c_d.p, (size_t)R * N * 4, cudaMemcpyDeviceToHost));
+  return 0;
 }
 
 int ani_halo_pack_x(ani_ctx* c, const void* x_dev, int is_float, const int64_t* send_index_dev, const void* shift_dev,

@@ -52,6 +52,8 @@ def load_library():
     L.ani_compute.argtypes = [vp, vp, vp, vp, vp, vp]
     L.ani_compute_device.argtypes = [vp, vp, i32, vp, i32, vp, vp, vp]
     L.ani_debug_get_aev.argtypes = [vp, vp, vp]
+    L.ani_debug_tc_gemm.argtypes = [i32, i32, i32, i32, vp, vp, vp, i32]
+    L.ani_debug_tc_gemm.restype = i32
     L.ani_halo_pack_x.argtypes = [vp, vp, i32, vp, vp, i64, vp]
     L.ani_halo_unpack_add_f.argtypes = [vp, vp, i32, vp, vp, i64]
     for name in ("ani_model_load", "ani_model_info", "ani_ctx_create", "ani_ctx_set_mlp_mode", "ani_ctx_set_stream",
@@ -67,8 +69,18 @@ EXPORTED_SYMBOLS = [
     "ani_model_load", "ani_model_free", "ani_model_info", "ani_ctx_create", "ani_ctx_destroy", "ani_ctx_set_mlp_mode",
     "ani_ctx_set_stream", "ani_ctx_synchronize", "ani_set_neighbors_full", "ani_set_neighbors_half", "ani_compute",
     "ani_compute_device", "ani_halo_pack_x", "ani_halo_unpack_add_f", "ani_debug_get_aev", "ani_last_timing",
-    "ani_ctx_enable_timing", "ani_last_error", "ani_abi_version",
+    "ani_ctx_enable_timing", "ani_last_error", "ani_abi_version", "ani_debug_tc_gemm",
 ]
+
+
+def debug_tc_gemm(A, B, three_pass: bool = True, device: int = 0):
+    """C = A @ B.T through the tcgen05 GEMM kernel (test hook)."""
+    A = np.ascontiguousarray(A, dtype=np.float32)
+    B = np.ascontiguousarray(B, dtype=np.float32)
+    Cm = np.empty((A.shape[0], B.shape[0]), dtype=np.float32)
+    _check(load_library().ani_debug_tc_gemm(device, A.shape[0], B.shape[0], A.shape[1], A.ctypes.data, B.ctypes.data,
+                                            Cm.ctypes.data, int(three_pass)))
+    return Cm
 
 
 def _check(rc: int):
