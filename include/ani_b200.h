@@ -53,8 +53,11 @@ int ani_ctx_create(const ani_model* model, int device, int use_num_models, int u
 void ani_ctx_destroy(ani_ctx* ctx);
 int ani_ctx_set_mlp_mode(ani_ctx* ctx, int mode); /* enum ani_mlp_mode; single precision only */
 /* Run on the caller's CUDA stream (cudaStream_t as void*) instead of the context's own, so device-resident
- * callers (ani/kk, the multi-GPU halo exchange) keep stream order with their own kernels / NCCL. */
+ * callers (ani/kk, the multi-GPU halo exchange) keep stream order with their own kernels / NCCL.  The handle is
+ * used verbatim: NULL means the CUDA legacy default stream (what Kokkos and torch use by default), not "unset";
+ * ani_ctx_reset_stream goes back to the context's own non-blocking stream. */
 int ani_ctx_set_stream(ani_ctx* ctx, void* cuda_stream);
+int ani_ctx_reset_stream(ani_ctx* ctx);
 int ani_ctx_synchronize(ani_ctx* ctx);
 
 /* ---- neighbour data: call when the list was rebuilt (neighbor->ago == 0, pair_ani.cpp:107-151) ---------

@@ -588,7 +588,13 @@ int ani_ctx_set_mlp_mode(ani_ctx* c, int mode) {
 
 int ani_ctx_set_stream(ani_ctx* c, void* s) {
   if (!c) { set_error("null context"); return 1; }
-  c->stream = s ? (cudaStream_t)s : c->own_stream;
+  c->stream = (cudaStream_t)s;   // NULL is a real stream too: the legacy default stream (torch's default)
+  return 0;
+}
+
+int ani_ctx_reset_stream(ani_ctx* c) {
+  if (!c) { set_error("null context"); return 1; }
+  c->stream = c->own_stream;
   return 0;
 }
 

@@ -45,6 +45,7 @@ def load_library():
     L.ani_ctx_set_mlp_mode.argtypes = [vp, i32]
     L.ani_ctx_set_stream.argtypes = [vp, vp]
     L.ani_ctx_synchronize.argtypes = [vp]
+    L.ani_ctx_reset_stream.argtypes = [vp]
     L.ani_ctx_enable_timing.argtypes = [vp, i32]
     L.ani_last_timing.argtypes = [vp, C.POINTER(C.c_float), C.POINTER(i32)]
     L.ani_set_neighbors_full.argtypes = [vp, i32, i32, vp, i32, vp, vp, vp, i64, i32]
@@ -57,7 +58,7 @@ def load_library():
     L.ani_halo_pack_x.argtypes = [vp, vp, i32, vp, vp, i64, vp]
     L.ani_halo_unpack_add_f.argtypes = [vp, vp, i32, vp, vp, i64]
     for name in ("ani_model_load", "ani_model_info", "ani_ctx_create", "ani_ctx_set_mlp_mode", "ani_ctx_set_stream",
-                 "ani_ctx_synchronize", "ani_ctx_enable_timing", "ani_last_timing", "ani_set_neighbors_full",
+                 "ani_ctx_reset_stream", "ani_ctx_synchronize", "ani_ctx_enable_timing", "ani_last_timing", "ani_set_neighbors_full",
                  "ani_set_neighbors_half", "ani_compute", "ani_compute_device", "ani_debug_get_aev",
                  "ani_halo_pack_x", "ani_halo_unpack_add_f"):
         getattr(L, name).restype = i32
@@ -67,7 +68,7 @@ def load_library():
 
 EXPORTED_SYMBOLS = [
     "ani_model_load", "ani_model_free", "ani_model_info", "ani_ctx_create", "ani_ctx_destroy", "ani_ctx_set_mlp_mode",
-    "ani_ctx_set_stream", "ani_ctx_synchronize", "ani_set_neighbors_full", "ani_set_neighbors_half", "ani_compute",
+    "ani_ctx_set_stream", "ani_ctx_reset_stream", "ani_ctx_synchronize", "ani_set_neighbors_full", "ani_set_neighbors_half", "ani_compute",
     "ani_compute_device", "ani_halo_pack_x", "ani_halo_unpack_add_f", "ani_debug_get_aev", "ani_last_timing",
     "ani_ctx_enable_timing", "ani_last_error", "ani_abi_version", "ani_debug_tc_gemm",
 ]
@@ -135,7 +136,11 @@ class ANI:
         _check(self._L.ani_ctx_set_mlp_mode(self._ctx, mode))
 
     def set_stream(self, cuda_stream_ptr: Optional[int]):
-        _check(self._L.ani_ctx_set_stream(self._ctx, C.c_void_p(cuda_stream_ptr or 0)))
+        """Run on this cudaStream_t (0 = the legacy default stream); None = back to the context's own stream."""
+        if cuda_stream_ptr is None:
+            _check(self._L.ani_ctx_reset_stream(self._ctx))
+        else:
+            _check(self._L.ani_ctx_set_stream(self._ctx, C.c_void_p(cuda_stream_ptr)))
 
     def synchronize(self):
         _check(self._L.ani_ctx_synchronize(self._ctx))
