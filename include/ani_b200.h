@@ -72,6 +72,18 @@ int ani_set_neighbors_full(ani_ctx* ctx, int nlocal, int ntotal, const int* spec
 int ani_set_neighbors_half(ani_ctx* ctx, int nlocal, int ntotal, const int* species, int64_t npairs,
                            const int64_t* atom_index12, int on_device);
 
+/* Padded neighbour table as LAMMPS' KOKKOS package keeps it (pair_ani_kokkos.cpp:114-169): table entry (i, k) lives at
+ * table[i*row_stride + k*col_stride] (LayoutLeft: row_stride 1, col_stride = extent(0); LayoutRight: row_stride =
+ * max_neighs, col_stride 1).  types[ntotal] are LAMMPS types; species = types[i] - type_offset (1 for LAMMPS).  The
+ * table is de-padded ON THE DEVICE into the same flat list ani_set_neighbors_full takes (entries & neighmask), once per
+ * rebuild instead of the reference's per-step masked_select.  on_device: all pointers are device pointers.            */
+int ani_set_neighbors_table(ani_ctx* ctx, int nlocal, int ntotal, const int* types, int type_offset, int inum,
+                            const int* ilist, const int* numneigh, const int* table, int64_t row_stride,
+                            int64_t col_stride, int neighmask, int on_device);
+
+/* Number of usable CUDA devices (rank -> GPU mapping of the pair style, pair_ani.cpp:255-283). */
+int ani_device_count(int* out);
+
 /* ---- one timestep, host arrays (plain `ani` style; ANI::compute host overloads ani.cpp:100-265) ---------
  * x[ntotal][3] doubles.  out_energy: sum over LOCAL atoms.  out_force[ntotal][3] is OVERWRITTEN with the
  * force on local and ghost atoms (the caller folds ghosts back: pair_ani.cpp:197-210).  out_eatom[nlocal]

@@ -557,7 +557,10 @@ int ani_ctx_create(const ani_model* model, int device, int use_num_models, int u
   if (rc) return rc;
   const char* mode = getenv("ANI_B200_MLP_MODE");
   if (c->use_single) {
-    c->mlp_mode = ANI_MLP_FP32_SIMT;
+    // default: the tensor-core path that keeps fp32 parity, when every network's widths fit it; FFMA otherwise
+    c->mlp_mode = ANI_MLP_TF32X3;
+    for (int s = 0; s < model->hm.S; s++)
+      if (!tc::tc_supported_dims(model->hm.dims[s])) c->mlp_mode = ANI_MLP_FP32_SIMT;
     if (getenv("LAMMPS_ANI_ALLOW_TF32") && atoi(getenv("LAMMPS_ANI_ALLOW_TF32")) != 0) c->mlp_mode = ANI_MLP_TF32;  // ani.cpp:41-43
     if (mode) {
       if (!strcmp(mode, "simt")) c->mlp_mode = ANI_MLP_FP32_SIMT;
@@ -650,6 +653,67 @@ int ani_set_neighbors_full(ani_ctx* c, int nlocal, int ntotal, const int* specie
   if (run != npairs) { set_error("npairs does not match the sum of numneigh over ilist"); return 1; }
   return c->eng->set_neighbors(nlocal, ntotal, c->h_species.data(), c->h_beg.data(), c->h_cnt.data(), jlist, npairs,
                                on_device != 0);
+}
+
+int ani_device_count(int* out) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); n = 0; }
+  if (out) *out = n;
+  if (n == 0) { set_error("no CUDA device available (libani_b200 has no CPU fallback)"); return 1; }
+  return 0;
+}
+
+int ani_set_neighbors_table(ani_ctx* c, int nlocal, int ntotal, const int* types, int type_offset, int inum, const int* ilist,
+                            const int* numneigh, const int* table, int64_t row_stride, int64_t col_stride, int neighmask,
+                            int on_device) {
+  if (!c || !types || (inum > 0 && (!ilist || !numneigh || !table))) { set_error("ani_set_neighbors_table: null argument"); return 1; }
+  if (!c->use_fullnbr) { set_error("context was created for a half neighbour list"); return 1; }
+  if (nlocal < 0 || ntotal < nlocal || inum < 0 || inum > nlocal) { set_error("ani_set_neighbors_table: inconsistent sizes"); return 1; }
+  ANIB_CUDA_OK(cudaSetDevice(c->device));
+  if (fetch_ints(c->h_species, types, ntotal, on_device)) return 1;
+  for (int i = 0; i < ntotal; i++) c->h_species[i] -= type_offset;
+  std::vector<int> il, nn;
+  if (fetch_ints(il, ilist, inum, on_device)) return 1;
+  if (fetch_ints(nn, numneigh, nlocal, on_device)) return 1;
+  c->h_beg.assign(std::max(nlocal, 1), 0);
+  c->h_cnt.assign(std::max(nlocal, 1), 0);
+  int64_t run = 0;
+  int maxn = 0;
+  for (int ii = 0; ii < inum; ii++) {
+    const int i = il[ii];
+    if (i < 0 || i >= nlocal) { set_error("ilist entry outside the local atoms"); return 1; }
+    c->h_beg[i] = run;
+    c->h_cnt[i] = nn[i];
+    run += nn[i];
+    maxn = std::max(maxn, nn[i]);
+  }
+  // de-pad on the device: table (device, or uploaded once) -> flat list in the context's scratch
+  int *d_tab = nullptr, *d_flat = nullptr, *d_cnt = nullptr;
+  int64_t* d_beg = nullptr;
+  const int* tab = table;
+  const size_t tab_elems = (size_t)((int64_t)(nlocal > 0 ? nlocal - 1 : 0) * row_stride + (int64_t)(maxn > 0 ? maxn - 1 : 0) * col_stride + 1);
+  int rc = 0;
+  auto cleanup = [&]() { cudaFree(d_tab); cudaFree(d_flat); cudaFree(d_cnt); cudaFree(d_beg); };
+#define TAB_OK(expr) do { if ((expr) != cudaSuccess) { set_error(std::string(#expr) + " failed: " + cudaGetErrorString(cudaGetLastError())); cleanup(); return 1; } } while (0)
+  if (!on_device && run > 0) {
+    TAB_OK(cudaMalloc(&d_tab, tab_elems * sizeof(int)));
+    TAB_OK(cudaMemcpy(d_tab, table, tab_elems * sizeof(int), cudaMemcpyHostToDevice));
+    tab = d_tab;
+  }
+  TAB_OK(cudaMalloc(&d_flat, std::max<int64_t>(run, 1) * sizeof(int)));
+  TAB_OK(cudaMalloc(&d_cnt, std::max(nlocal, 1) * sizeof(int)));
+  TAB_OK(cudaMalloc(&d_beg, std::max(nlocal, 1) * sizeof(int64_t)));
+  TAB_OK(cudaMemcpy(d_cnt, c->h_cnt.data(), std::max(nlocal, 1) * sizeof(int), cudaMemcpyHostToDevice));
+  TAB_OK(cudaMemcpy(d_beg, c->h_beg.data(), std::max(nlocal, 1) * sizeof(int64_t), cudaMemcpyHostToDevice));
+  if (run > 0) {
+    depad_neighbors_kernel<<<(unsigned)(((int64_t)nlocal * 32 + 255) / 256), 256, 0, c->stream>>>(tab, row_stride, col_stride, d_beg,
+                                                                                                 d_cnt, nlocal, neighmask, d_flat);
+    TAB_OK(cudaStreamSynchronize(c->stream));
+  }
+#undef TAB_OK
+  rc = c->eng->set_neighbors(nlocal, ntotal, c->h_species.data(), c->h_beg.data(), c->h_cnt.data(), d_flat, run, true);
+  cleanup();
+  return rc;
 }
 
 int ani_set_neighbors_half(ani_ctx* c, int nlocal, int ntotal, const int* species, int64_t npairs,

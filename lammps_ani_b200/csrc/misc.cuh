@@ -41,4 +41,15 @@ __global__ void halo_unpack_add_kernel(T* __restrict__ f, const int64_t* __restr
   atomicAdd(f + idx[k] * 3 + cpt, buf[t]);
 }
 
+// padded neighbour table -> flat list (one warp per centre atom): jlist[beg[i] + k] = table[i*rs + k*cs] & mask
+__global__ void depad_neighbors_kernel(const int* __restrict__ table, int64_t rs, int64_t cs, const int64_t* __restrict__ beg,
+                                       const int* __restrict__ cnt, int nlocal, int mask, int* __restrict__ jlist) {
+  const int i = (int)(((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5);
+  const int lane = threadIdx.x & 31;
+  if (i >= nlocal) return;
+  const int64_t b = beg[i];
+  const int n = cnt[i];
+  for (int k = lane; k < n; k += 32) jlist[b + k] = table[(int64_t)i * rs + (int64_t)k * cs] & mask;
+}
+
 }  // namespace anib

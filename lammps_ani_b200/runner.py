@@ -50,6 +50,8 @@ def load_library():
     L.ani_last_timing.argtypes = [vp, C.POINTER(C.c_float), C.POINTER(i32)]
     L.ani_set_neighbors_full.argtypes = [vp, i32, i32, vp, i32, vp, vp, vp, i64, i32]
     L.ani_set_neighbors_half.argtypes = [vp, i32, i32, vp, i64, vp, i32]
+    L.ani_set_neighbors_table.argtypes = [vp, i32, i32, vp, i32, i32, vp, vp, vp, i64, i64, i32, i32]
+    L.ani_device_count.argtypes = [C.POINTER(i32)]
     L.ani_compute.argtypes = [vp, vp, vp, vp, vp, vp]
     L.ani_compute_device.argtypes = [vp, vp, i32, vp, i32, vp, vp, vp]
     L.ani_debug_get_aev.argtypes = [vp, vp, vp]
@@ -59,8 +61,8 @@ def load_library():
     L.ani_halo_unpack_add_f.argtypes = [vp, vp, i32, vp, vp, i64]
     for name in ("ani_model_load", "ani_model_info", "ani_ctx_create", "ani_ctx_set_mlp_mode", "ani_ctx_set_stream",
                  "ani_ctx_reset_stream", "ani_ctx_synchronize", "ani_ctx_enable_timing", "ani_last_timing", "ani_set_neighbors_full",
-                 "ani_set_neighbors_half", "ani_compute", "ani_compute_device", "ani_debug_get_aev",
-                 "ani_halo_pack_x", "ani_halo_unpack_add_f"):
+                 "ani_set_neighbors_half", "ani_set_neighbors_table", "ani_device_count", "ani_compute",
+                 "ani_compute_device", "ani_debug_get_aev", "ani_halo_pack_x", "ani_halo_unpack_add_f"):
         getattr(L, name).restype = i32
     _lib = L
     return L
@@ -70,7 +72,8 @@ EXPORTED_SYMBOLS = [
     "ani_model_load", "ani_model_free", "ani_model_info", "ani_ctx_create", "ani_ctx_destroy", "ani_ctx_set_mlp_mode",
     "ani_ctx_set_stream", "ani_ctx_reset_stream", "ani_ctx_synchronize", "ani_set_neighbors_full", "ani_set_neighbors_half", "ani_compute",
     "ani_compute_device", "ani_halo_pack_x", "ani_halo_unpack_add_f", "ani_debug_get_aev", "ani_last_timing",
-    "ani_ctx_enable_timing", "ani_last_error", "ani_abi_version", "ani_debug_tc_gemm",
+    "ani_ctx_enable_timing", "ani_last_error", "ani_abi_version", "ani_debug_tc_gemm", "ani_set_neighbors_table",
+    "ani_device_count",
 ]
 
 
@@ -170,6 +173,21 @@ class ANI:
         self.nlocal, self.ntotal = int(nlocal), int(species.shape[0])
         _check(self._L.ani_set_neighbors_half(self._ctx, self.nlocal, self.ntotal, _ptr(species), int(a.shape[1]),
                                               _ptr(a), 0))
+
+    def set_neighbors_table(self, types, ilist, numneigh, table, nlocal: int, layout_left: bool = False,
+                            neighmask: int = 0x1FFFFFFF):
+        """Padded [nrows][max_neighs] table as the KOKKOS package keeps it (pair_ani_kokkos.cpp:143-169); `types` are
+        LAMMPS types (1-based).  layout_left: the table memory is column-major."""
+        types = np.ascontiguousarray(types, dtype=np.int32)
+        ilist = np.ascontiguousarray(ilist, dtype=np.int32)
+        numneigh = np.ascontiguousarray(numneigh, dtype=np.int32)
+        table = np.asarray(table, dtype=np.int32)
+        nrows, maxn = table.shape
+        mem = np.ascontiguousarray(table.T if layout_left else table)
+        rs, cs = (1, nrows) if layout_left else (maxn, 1)
+        self.nlocal, self.ntotal = int(nlocal), int(types.shape[0])
+        _check(self._L.ani_set_neighbors_table(self._ctx, self.nlocal, self.ntotal, _ptr(types), 1, int(ilist.shape[0]),
+                                               _ptr(ilist), _ptr(numneigh), _ptr(mem), rs, cs, neighmask, 0))
 
     # ---- one step, host arrays (ani.cpp:100-265)
     def compute(self, species, coordinates, *nbr, nlocal: int, ago: int = 0, atomic: bool = False, vflag: bool = False):
