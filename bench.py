@@ -41,7 +41,7 @@ def parse_args():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--atoms", type=int, default=int(os.environ.get("ANI_BENCH_ATOMS", 300000)), help="atoms per GPU")
     ap.add_argument("--models", type=int, default=8)
-    ap.add_argument("--mlp-mode", default=os.environ.get("ANI_B200_MLP_MODE", ""), help="simt | tf32x3 | tf32")
+    ap.add_argument("--mlp-mode", default=os.environ.get("ANI_B200_MLP_MODE", ""), help="simt | tf32x3 | tf32 | f16x3 (default: the library default, f16x3)")
     ap.add_argument("--cpu-sample-atoms", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     return ap.parse_args()
@@ -208,7 +208,9 @@ def main():
     cells, box, sub, halo, il, nn, jl = build_system(args.atoms, grid, rank)
     M = args.models
     ani = runner.ANI(model, local_rank, M, use_cuaev=True, use_fullnbr=True, use_single=True)
-    mode_names = {"simt": runner.MLP_FP32_SIMT, "tf32x3": runner.MLP_TF32X3, "tf32": runner.MLP_TF32}
+    mode_names = {"simt": runner.MLP_FP32_SIMT, "tf32x3": runner.MLP_TF32X3, "tf32": runner.MLP_TF32, "f16x3": runner.MLP_F16X3}
+    if not args.mlp_mode:
+        args.mlp_mode = "f16x3"
     if args.mlp_mode:
         ani.set_mlp_mode(mode_names[args.mlp_mode])
     step = GpuDomainStep(ani, sub, halo, dev, il, nn, jl)
@@ -282,16 +284,19 @@ def main():
         which = "MEASURED_PEAKS.json" if peaks else "fallback (B200_PROFILING.md)"
         fl = flops_per_step(params, sub.species[:nlocal], M)
         mlp_ms = max(stage[2], 1e-9)
-        mode = {0: "fp32 FFMA (SIMT)", 1: "tcgen05 tf32x3", 2: "tcgen05 tf32"}.get(
+        mode = {0: "fp32 FFMA (SIMT)", 1: "tcgen05 tf32x3", 2: "tcgen05 tf32", 3: "tcgen05 f16x3"}.get(
             mode_names.get(args.mlp_mode, 0), "?")
-        tf32_peak = bf16 / 2.0
+        passes = {0: 1, 1: 3, 2: 1, 3: 3}[mode_names.get(args.mlp_mode, 0)]
+        tf32_peak = bf16 if args.mlp_mode == "f16x3" else bf16 / 2.0
         ach = fl / (mlp_ms * 1e-3) / 1e12
         L = params.aev_length
         aev_bytes = nlocal * (4.0 * float(jl.size) / nlocal + 8 + 16 + 4 * L)       # list + x + AEV row store
         bwd_bytes = nlocal * (4.0 * L + 4.0 * float(jl.size) / nlocal + 16 + 12)
         roofline = {"kernel": f"ensemble MLP fwd+bwd GEMM stage ({mode})", "bound": "tensor", "achieved": ach,
                     "peak": tf32_peak, "unit": "TFLOP/s", "frac": ach / tf32_peak, "traffic": None,
-                    "peak_source": f"{which}: bf16_tflops_sustained/2 taken as the dense TF32 peak",
+                    "peak_source": (f"{which}: bf16_tflops_sustained (fp16 runs at the bf16 rate)" if args.mlp_mode == "f16x3"
+                                    else f"{which}: bf16_tflops_sustained/2 taken as the dense TF32 peak"),
+                    "issued_flops_factor": passes, "frac_issued": passes * ach / tf32_peak,
                     "algorithmic_flops_per_step": fl, "ms": mlp_ms}
         stages = {"pack_ms": stage[0], "aev_fwd_ms": stage[1], "mlp_ms": stage[2], "aev_bwd_ms": stage[3], "reduce_d2h_ms": stage[4],
                   "aev_fwd_GBps": aev_bytes / (max(stage[1], 1e-9) * 1e-3) / 1e9, "aev_bwd_GBps": bwd_bytes / (max(stage[3], 1e-9) * 1e-3) / 1e9,

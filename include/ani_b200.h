@@ -30,6 +30,8 @@ enum ani_mlp_mode {
   ANI_MLP_FP32_SIMT = 0, /* FFMA GEMMs, fp32 accumulate: the strict reference-precision path (and fp64 mode)   */
   ANI_MLP_TF32X3 = 1,    /* tcgen05.mma kind::tf32, 3-pass hi/lo split, fp32 accumulate in TMEM (~fp32 accuracy) */
   ANI_MLP_TF32 = 2,      /* single-pass TF32 on tcgen05 -- the reference's LAMMPS_ANI_ALLOW_TF32=1 (ani.cpp:41-43) */
+  ANI_MLP_F16X3 = 3,     /* tcgen05.mma kind::f16 on scaled fp16 hi/lo planes, 3-pass, fp32 accumulate (~fp32 accuracy,
+                            twice the TF32x3 rate): the default when the network widths allow it                       */
 };
 
 /* ---- model parameters ------------------------------------------------------------------------------
@@ -117,7 +119,7 @@ int ani_last_timing(ani_ctx* ctx, float stage_ms[5], int* num_launches);
 int ani_ctx_enable_timing(ani_ctx* ctx, int on);
 
 /* Test hook for the tensor-core GEMM kernel alone: C[R][N] = A[R][K] . B[N][K]^T (host pointers, row major),
- * three_pass = 1: TF32x3 split, 0: single TF32.  N must have a divisor <= 256 that is a multiple of 16; K % 8 == 0. */
+ * three_pass = 1: TF32x3 split, 0: single TF32, 2: the fp16 hi/lo (F16X3) kernel.  N must have a divisor <= 256 that is a multiple of 16; K % 8 == 0. */
 int ani_debug_tc_gemm(int device, int R, int N, int K, const float* A, const float* B, float* C, int three_pass);
 
 const char* ani_last_error(void);

@@ -15,6 +15,8 @@
 // cos(theta - ShfZ) is expanded as cos(theta)cos(ShfZ) + sin(theta)sin(ShfZ) with cos(theta) = 0.95 cos_jik,
 // which is the same function as the reference's acos/cos pair without the two transcendental calls.
 #pragma once
+#include <cuda_fp16.h>
+
 #include "common.cuh"
 
 namespace anib {
@@ -153,8 +155,8 @@ aev_forward_kernel(const __grid_constant__ AevConst<T> P, int radial_filter,
                    const typename Vec4T<T>::type* __restrict__ x4, const int64_t* __restrict__ nbr_beg,
                    const int* __restrict__ nbr_cnt, const int* __restrict__ jlist, const int* __restrict__ order,
                    int nrows, T* __restrict__ aev,
-                   int64_t ld, float* __restrict__ aev_hi, float* __restrict__ aev_lo, int64_t ld_planes, int cap,
-                   int capA, int smem_per_warp, int* __restrict__ errflag) {
+                   int64_t ld, void* __restrict__ aev_hi, void* __restrict__ aev_lo, int64_t ld_planes, int plane_mode,
+                   float plane_scale, int cap, int capA, int smem_per_warp, int* __restrict__ errflag) {
   using V4 = typename Vec4T<T>::type;
   extern __shared__ __align__(32) unsigned char smem_raw[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -219,18 +221,24 @@ aev_forward_kernel(const __grid_constant__ AevConst<T> P, int radial_filter,
     }
   }
   __syncwarp();
-  // ---- one coalesced store of the row
-  T* out = aev + (size_t)row * ld;
+  // ---- one coalesced store of the row: fp32/fp64 row (aev != nullptr) and / or operand planes for the tensor-core MLP
+  // (plane_mode 1: TF32 hi/lo in fp32 containers; 2: fp16 hi/lo of plane_scale * value)
+  T* out = aev ? aev + (size_t)row * ld : nullptr;
   for (int t = lane; t < P.aev_len; t += 32) {
     T v = acc[t];
     if (t < P.rad_len)
       for (int s2 = 1; s2 < npl; s2++) v += acc[P.aev_len + (s2 - 1) * P.rad_len + t];
-    out[t] = v;
-    if (aev_hi != nullptr) {
+    if (out) out[t] = v;
+    if (plane_mode == 1) {
       float f = (float)v;
       float hi = round_tf32(f);
-      aev_hi[(size_t)row * ld_planes + t] = hi;
-      aev_lo[(size_t)row * ld_planes + t] = round_tf32(f - hi);
+      ((float*)aev_hi)[(size_t)row * ld_planes + t] = hi;
+      ((float*)aev_lo)[(size_t)row * ld_planes + t] = round_tf32(f - hi);
+    } else if (plane_mode == 2) {
+      const float f = (float)v * plane_scale;
+      const __half hi = __float2half_rn(f);
+      ((__half*)aev_hi)[(size_t)row * ld_planes + t] = hi;
+      ((__half*)aev_lo)[(size_t)row * ld_planes + t] = __float2half_rn(f - __half2float(hi));
     }
   }
 }

@@ -16,6 +16,7 @@
 #include "common.cuh"
 #include "misc.cuh"
 #include "mlp_simt.cuh"
+#include "mlp_f16.cuh"
 #include "mlp_tc.cuh"
 
 namespace anib {
@@ -79,6 +80,7 @@ struct SpeciesNet {
   std::vector<DevBuf> WT;     // [l] (1 <= l < nl-1): [M][in][out]  (operand of the backward GEMMs)
   DevBuf W1cat;               // [L][M*h1]: W1cat[n][m*h1+k] = W1_m[k][n]
   TcSpeciesWeights tc;        // TF32 hi/lo planes for the tcgen05 path (fp32 only)
+  f16::SpeciesWeights hw;     // scaled fp16 hi/lo planes for the f16x3 tcgen05 path (fp32 only)
 };
 
 }  // namespace anib
@@ -128,6 +130,8 @@ struct Engine : EngineBase {
   DevBuf d_aev_hi, d_aev_lo;
   DevBuf d_H, d_D, d_G;   // MLP intermediates of one chunk
   TcWork tcw;
+  f16::Work hwork;
+  int64_t ld_planes = 0;   // row pitch of the fp16 AEV planes (multiple of 8 halves = 16 bytes for TMA)
   PinnedBuf h_x, h_f, h_small;
   int64_t ld_aev = 0;
   int chunk_rows = 2048;
@@ -152,6 +156,7 @@ struct Engine : EngineBase {
     for (int s = 0; s < hm.S; s++)
       for (int t = s; t < hm.S; t++) { P.triu[s][t] = p; P.triu[t][s] = p; p++; }
     ld_aev = (P.aev_len + 3) / 4 * 4;
+    ld_planes = (P.aev_len + 7) / 8 * 8;
     // ---- upload weights in the arithmetic type
     nets.resize(hm.S);
     for (int s = 0; s < hm.S; s++) {
@@ -308,6 +313,8 @@ struct Engine : EngineBase {
   }
 
   int mlp_tc_species(int s, int row0, int R);   // defined for float below
+  int mlp_f16_species(int s, int row0, int R);
+  bool aev_in_planes = false;
 
   // ---------------------------------------------------------------------------------------------- one step
   int compute(const void* x, bool x_on_device, bool x_is_float, double* out_energy, double* out_force_host, void* f_dev,
@@ -337,22 +344,33 @@ struct Engine : EngineBase {
     if (want_virial) ANIB_CUDA_OK(cudaMemsetAsync(d_virial.p, 0, kVirialSlots * 9 * sizeof(double), st));
     if (tm) cudaEventRecord(c->ev[1], st);
     // ---- (1) AEV forward
-    const bool tc_mode = (sizeof(T) == 4) && c->mlp_mode != ANI_MLP_FP32_SIMT;
+    const bool f16_mode = (sizeof(T) == 4) && c->mlp_mode == ANI_MLP_F16X3;
+    const bool tc_mode = (sizeof(T) == 4) && c->mlp_mode != ANI_MLP_FP32_SIMT && !f16_mode;
+    aev_in_planes = f16_mode;
     const int npl = 32 / (P.nR <= 16 ? 16 : 32);
     if (nlocal > 0) {
       const int acc_f = P.aev_len + (npl - 1) * P.rad_len;
       AevSmemLayout Lf = aev_smem_layout<T>(cap, capA, acc_f, false);
       const int smem = Lf.bytes * kAevWarps;
       ANIB_CUDA_OK(cudaFuncSetAttribute(aev_forward_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-      float *hi = nullptr, *lo = nullptr;
-      if (tc_mode) {
+      void *hi = nullptr, *lo = nullptr;
+      int plane_mode = 0;
+      int64_t ldp = ld_aev;
+      T* rows = d_aev.as<T>();
+      if (f16_mode) {
+        ANIB_RESERVE(d_aev_hi, (size_t)f16::padded_rows(nlocal) * ld_planes * sizeof(__half));
+        ANIB_RESERVE(d_aev_lo, (size_t)f16::padded_rows(nlocal) * ld_planes * sizeof(__half));
+        hi = d_aev_hi.p; lo = d_aev_lo.p; plane_mode = 2; ldp = ld_planes;
+        rows = nullptr;   // the fp32 rows are not needed: the MLP reads the planes (get_aev rebuilds them from the planes)
+      } else if (tc_mode) {
         ANIB_RESERVE(d_aev_hi, (size_t)tc_padded_rows(nlocal, hm.S) * ld_aev * sizeof(float));
         ANIB_RESERVE(d_aev_lo, (size_t)tc_padded_rows(nlocal, hm.S) * ld_aev * sizeof(float));
-        hi = d_aev_hi.as<float>(); lo = d_aev_lo.as<float>();
+        hi = d_aev_hi.p; lo = d_aev_lo.p; plane_mode = 1;
       }
       aev_forward_kernel<T><<<(nlocal + kAevWarps - 1) / kAevWarps, kAevWarps * 32, smem, st>>>(
           P, c->use_cuaev ? 1 : 0, d_x4.as<V4>(), d_beg.as<int64_t>(), d_cnt.as<int>(), d_jlist.as<int>(),
-          d_order.as<int>(), nlocal, d_aev.as<T>(), ld_aev, hi, lo, ld_aev, cap, capA, Lf.bytes, d_err.as<int>());
+          d_order.as<int>(), nlocal, rows, ld_aev, hi, lo, ldp, plane_mode, f16::kScaleAev, cap, capA, Lf.bytes,
+          d_err.as<int>());
       c->launches++;
     }
     if (tm) cudaEventRecord(c->ev[2], st);
@@ -360,7 +378,7 @@ struct Engine : EngineBase {
     for (int s = 0; s < hm.S; s++) {
       const int R = boff[s + 1] - boff[s];
       if (R == 0) continue;
-      int rc = tc_mode ? mlp_tc_species(s, boff[s], R) : mlp_simt_species(s, boff[s], R);
+      int rc = f16_mode ? mlp_f16_species(s, boff[s], R) : tc_mode ? mlp_tc_species(s, boff[s], R) : mlp_simt_species(s, boff[s], R);
       if (rc) return rc;
     }
     if (tm) cudaEventRecord(c->ev[3], st);
@@ -468,6 +486,18 @@ struct Engine : EngineBase {
     for (int pass = 0; pass < 2; pass++) {
       double* out = pass == 0 ? aev : daev;
       if (!out) continue;
+      if (pass == 0 && aev_in_planes) {   // f16x3 mode keeps the AEV only as scaled fp16 hi/lo planes
+        std::vector<__half> ph((size_t)nlocal * ld_planes), pl((size_t)nlocal * ld_planes);
+        ANIB_CUDA_OK(cudaMemcpy(ph.data(), d_aev_hi.p, ph.size() * 2, cudaMemcpyDeviceToHost));
+        ANIB_CUDA_OK(cudaMemcpy(pl.data(), d_aev_lo.p, pl.size() * 2, cudaMemcpyDeviceToHost));
+        for (int pos = 0; pos < nlocal; pos++) {
+          const int i = h_order[pos];
+          for (int k = 0; k < P.aev_len; k++)
+            out[(size_t)i * P.aev_len + k] = ((double)__half2float(ph[(size_t)pos * ld_planes + k]) +
+                                              (double)__half2float(pl[(size_t)pos * ld_planes + k])) / (double)f16::kScaleAev;
+        }
+        continue;
+      }
       ANIB_CUDA_OK(cudaMemcpy(tmp.data(), pass == 0 ? d_aev.p : d_daev.p, tmp.size() * sizeof(T), cudaMemcpyDeviceToHost));
       for (int pos = 0; pos < nlocal; pos++) {
         const int i = h_order[pos];
@@ -481,6 +511,16 @@ struct Engine : EngineBase {
 template <> int Engine<double>::mlp_tc_species(int, int, int) {
   set_error("tensor-core MLP modes are single precision only");
   return 1;
+}
+
+template <> int Engine<double>::mlp_f16_species(int, int, int) {
+  set_error("tensor-core MLP modes are single precision only");
+  return 1;
+}
+
+template <> int Engine<float>::mlp_f16_species(int s, int row0, int R) {
+  return f16::mlp_species(c->stream, nets[s].hw, hwork, M, nets[s].dims, (const __half*)d_aev_hi.p, (const __half*)d_aev_lo.p,
+                          ld_planes, nlocal, row0, R, d_daev.as<float>(), ld_aev, d_eatom.as<double>(), hm.sae[s], &c->launches);
 }
 
 template <> int Engine<float>::mlp_tc_species(int s, int row0, int R) {
@@ -549,6 +589,7 @@ int ani_ctx_create(const ani_model* model, int device, int use_num_models, int u
     c->eng.reset(e);
     rc = e->init();
     for (int s = 0; s < model->hm.S && !rc; s++) rc = tc_prepare_species(model->hm, M, s, e->nets[s].tc);
+    for (int s = 0; s < model->hm.S && !rc; s++) rc = f16::prepare_species(model->hm, M, s, e->nets[s].hw);
   } else {
     auto* e = new Engine<double>(c.get(), model->hm, M);
     c->eng.reset(e);
@@ -558,14 +599,18 @@ int ani_ctx_create(const ani_model* model, int device, int use_num_models, int u
   const char* mode = getenv("ANI_B200_MLP_MODE");
   if (c->use_single) {
     // default: the tensor-core path that keeps fp32 parity, when every network's widths fit it; FFMA otherwise
-    c->mlp_mode = ANI_MLP_TF32X3;
+    c->mlp_mode = ANI_MLP_F16X3;
     for (int s = 0; s < model->hm.S; s++)
-      if (!tc::tc_supported_dims(model->hm.dims[s])) c->mlp_mode = ANI_MLP_FP32_SIMT;
+      if (!f16::supported_dims(model->hm.dims[s])) c->mlp_mode = ANI_MLP_TF32X3;
+    if (c->mlp_mode == ANI_MLP_TF32X3)
+      for (int s = 0; s < model->hm.S; s++)
+        if (!tc::tc_supported_dims(model->hm.dims[s])) c->mlp_mode = ANI_MLP_FP32_SIMT;
     if (getenv("LAMMPS_ANI_ALLOW_TF32") && atoi(getenv("LAMMPS_ANI_ALLOW_TF32")) != 0) c->mlp_mode = ANI_MLP_TF32;  // ani.cpp:41-43
     if (mode) {
       if (!strcmp(mode, "simt")) c->mlp_mode = ANI_MLP_FP32_SIMT;
       else if (!strcmp(mode, "tf32x3")) c->mlp_mode = ANI_MLP_TF32X3;
       else if (!strcmp(mode, "tf32")) c->mlp_mode = ANI_MLP_TF32;
+      else if (!strcmp(mode, "f16x3")) c->mlp_mode = ANI_MLP_F16X3;
     }
   }
   *out = c.release();
@@ -583,7 +628,7 @@ void ani_ctx_destroy(ani_ctx* c) {
 
 int ani_ctx_set_mlp_mode(ani_ctx* c, int mode) {
   if (!c) { set_error("null context"); return 1; }
-  if (mode < 0 || mode > 2) { set_error("unknown MLP mode"); return 1; }
+  if (mode < 0 || mode > 3) { set_error("unknown MLP mode"); return 1; }
   if (!c->use_single && mode != ANI_MLP_FP32_SIMT) { set_error("tensor-core MLP modes are single precision only"); return 1; }
   c->mlp_mode = mode;
   return 0;
@@ -770,8 +815,39 @@ int ani_debug_get_aev(ani_ctx* c, double* aev, double* daev) {
   return c->eng->get_aev(aev, daev);
 }
 
+// test hook for the f16x3 kernel: C = A . B^T through EPI_D (fp32 rows out)
+static int debug_f16_gemm(int device, int R, int N, int K, const float* A, const float* B, float* C) {
+  using namespace anib::f16;
+  if (K % 16 != 0 || N % 4 != 0) { set_error("ani_debug_tc_gemm(f16x3): K must be a multiple of 16 and N of 4"); return 1; }
+  ANIB_CUDA_OK(cudaSetDevice(device));
+  std::vector<float> av(A, A + (size_t)R * K), bv(B, B + (size_t)N * K);
+  HalfPlanes a, b;
+  const float sa = pick_scale(av) / 64.f, sb = pick_scale(bv);
+  if (upload_half_planes(av, sa, a) || upload_half_planes(bv, sb, b)) return 1;
+  anib::DevBufTc c_d;
+  if (!c_d.reserve((size_t)R * N * 4)) { set_error("out of memory"); return 1; }
+  int num_sms = 0, max_smem = 0;
+  cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, device);
+  cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, device);
+  Launcher L{nullptr, num_sms, nullptr, max_smem};
+  Args g{};
+  g.BN = (N <= 256 && N % 32 == 0) ? N : 256;
+  g.R = R; g.N = N; g.num_n_tiles = (N + g.BN - 1) / g.BN; g.num_row_tiles = (R + BM - 1) / BM; g.K = K; g.batch = 1;
+  g.acc_scale = 1.0f / (sa * sb);
+  const Operand none{nullptr, nullptr, 0, 0, 0};
+  Operand Ao{a.h(), a.l(), (uint64_t)R, (uint64_t)K, (uint64_t)K}, Bo{b.h(), b.l(), (uint64_t)N, (uint64_t)K, (uint64_t)K};
+  if (launch_gemm<EPI_D>(L, Ao, Bo, none, c_d.f(), (uint64_t)R, (uint64_t)N, (uint64_t)N, none, g)) return 1;
+  ANIB_CUDA_OK(cudaDeviceSynchronize());
+  ANIB_CUDA_OK(cudaMemcpy(C, c_d.p, (size_t)R * N * 4, cudaMemcpyDeviceToHost));
+  return 0;
+}
+
 int ani_debug_tc_gemm(int device, int R, int N, int K, const float* A, const float* B, float* C, int three_pass) {
   using namespace anib::tc;
+  if (three_pass == 2) {
+    if (!A || !B || !C || R < 1 || N < 16 || K < 16) { set_error("ani_debug_tc_gemm: bad arguments"); return 1; }
+    return debug_f16_gemm(device, R, N, K, A, B, C);
+  }
   if (!A || !B || !C || R < 1 || N < 16 || K < 8 || K % 8 != 0 || pick_bn(N) == 0) { set_error("ani_debug_tc_gemm: bad arguments"); return 1; }
   ANIB_CUDA_OK(cudaSetDevice(device));
   DevBufTc a_hi, a_lo, b_hi, b_lo, c_d;

@@ -21,7 +21,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libani_b200.so")
 HARTREE2KCALMOL = 627.5094738898777
 
-MLP_FP32_SIMT, MLP_TF32X3, MLP_TF32 = 0, 1, 2
+MLP_FP32_SIMT, MLP_TF32X3, MLP_TF32, MLP_F16X3 = 0, 1, 2, 3
 
 _lib = None
 
@@ -77,8 +77,8 @@ EXPORTED_SYMBOLS = [
 ]
 
 
-def debug_tc_gemm(A, B, three_pass: bool = True, device: int = 0):
-    """C = A @ B.T through the tcgen05 GEMM kernel (test hook)."""
+def debug_tc_gemm(A, B, three_pass=True, device: int = 0):
+    """C = A @ B.T through the tcgen05 GEMM kernels (test hook): three_pass False = TF32, True = TF32x3, 2 = F16x3."""
     A = np.ascontiguousarray(A, dtype=np.float32)
     B = np.ascontiguousarray(B, dtype=np.float32)
     Cm = np.empty((A.shape[0], B.shape[0]), dtype=np.float32)

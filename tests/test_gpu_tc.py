@@ -71,3 +71,40 @@ def test_full_path_tf32_single_pass_has_its_own_tolerance(runner, ani2x_synth_pa
     print("tf32: force max err", np.abs(f - ref["forces"]).max(), "E rel", abs(e - ref["energy"]) / abs(ref["energy"]))
     assert abs(e - ref["energy"]) <= 1e-5 * abs(ref["energy"])
     assert np.abs(f - ref["forces"]).max() <= 5e-3 * EV2KCAL
+
+
+@pytest.mark.parametrize("R,N,K", [(128, 160, 32), (128, 256, 1008), (300, 192, 256), (1000, 1008, 2048), (77, 96, 160),
+                                   (5000, 224, 448)])
+def test_f16x3_gemm_matches_fp64(runner, R, N, K):
+    """fp16 hi/lo planes, three kind::f16 MMAs per k-step, TMA-store epilogue (ragged rows, ragged N tile, ragged last
+    k-block).  Same error budget as TF32x3."""
+    rng = np.random.default_rng(R + N + K)
+    A = (rng.standard_normal((R, K)) * np.exp(rng.uniform(-4, 2, size=(R, 1)))).astype(np.float32)   # rows of mixed magnitude
+    B = (rng.standard_normal((N, K)) * 0.05).astype(np.float32)
+    ref = A.astype(np.float64) @ B.astype(np.float64).T
+    C = runner.debug_tc_gemm(A, B, three_pass=2)
+    rowscale = np.sqrt((A.astype(np.float64) ** 2).sum(1, keepdims=True)) * 0.05
+    err = np.abs(C - ref) / rowscale
+    fp32 = np.abs((A @ B.T) - ref) / rowscale
+    print(f"\nR={R} N={N} K={K}: f16x3 err {err.max():.2e}  numpy fp32 err {fp32.max():.2e}")
+    assert err.max() < 1e-4
+
+
+@pytest.mark.parametrize("model", ["ani2x_synth", "ani1xnr"])
+def test_full_path_f16x3_parity(runner, ani2x_synth_path, ani1xnr_path, model):
+    path = ani2x_synth_path if model == "ani2x_synth" else ani1xnr_path
+    x, sp, box = domain.make_water_box((8, 9, 10), seed=7)
+    sub = domain.decompose(x, sp, box)[0]
+    il, nn, jl = domain.full_neighbor_list(sub.x, sub.nlocal)
+    ref = OracleANI(path).compute_full(sub.species, sub.x, il, nn, jl, sub.nlocal, single_coords=True, want_aev=True, want_daev=True)
+    ani = runner.ANI(path, 0, -1, True, True, True)
+    ani.set_mlp_mode(runner.MLP_F16X3)
+    e, f, eatom, virial = ani.compute(sub.species, sub.x, il, jl, nn, nlocal=sub.nlocal, ago=0, atomic=True, vflag=True)
+    aev, daev = ani.debug_aev()
+    print("f16x3: aev max err", np.abs(aev - ref["aev"]).max(), "daev max err", np.abs(daev - ref["daev"]).max(),
+          "force max err", np.abs(f - ref["forces"]).max(), "E rel err", abs(e - ref["energy"]) / abs(ref["energy"]))
+    assert np.abs(aev - ref["aev"]).max() <= 2e-5 * max(1.0, np.abs(ref["aev"]).max())
+    assert abs(e - ref["energy"]) <= 1e-6 * abs(ref["energy"])
+    assert np.abs(f - ref["forces"]).max() <= 1e-4 * EV2KCAL
+    assert np.abs(eatom - ref["eatom"]).max() <= 1e-5 * np.abs(ref["eatom"]).max()
+    assert np.abs(virial - ref["virial"]).max() <= 1e-4 * max(1.0, np.abs(ref["virial"]).max())
