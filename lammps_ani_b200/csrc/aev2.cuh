@@ -1,0 +1,425 @@
+// aev2.cuh -- second-generation AEV forward / backward kernels (one warp per centre atom, lanes = angular TRIPLES).
+//
+// Same contract as the kernels in aev.cuh (which stay as the reference implementation inside the library and are
+// selectable with ANI_B200_AEV=1); what changes is where the transcendental work is done.  An angular term factorises
+//     2 fc(r_a) fc(r_b) * f1_z(theta_ab) * f2_a((r_a + r_b)/2),      f1_z = ((1 + cos(theta - ShfZ_z))/2)^Zeta,
+//                                                                    f2_a = exp(-EtaA (ravg - ShfA_a)^2)
+// so a triple needs nZ powers and nA exponentials, not nZ*nA of each.  Forward: a batch of 32 triples is evaluated with
+// one triple per lane (stage 1: f1*fc and f2 into shared memory), then the nA*nZ products are accumulated with one
+// (ShfA,ShfZ) term per lane in registers (stage 2), flushing to the shared AEV row only when the species pair changes.
+// Backward: one triple per lane computes both neighbours' gradients at once from the factorised sums
+//     S0 = sum w f1 f2, S1 = sum w f1 f2', S2 = sum w f1' f2        (w = dE/dAEV of the triple's species pair)
+// and adds them to the per-neighbour gradient in shared memory; triples are enumerated along wrapped diagonals
+// (a, (a+k) mod n) so the lanes of a batch touch distinct neighbours and the shared-memory atomics do not serialise.
+// Replaces cuaev's angular kernels K2/K9 reached via models/lammps_ani.py:277 and :203-214.
+#pragma once
+#include "aev.cuh"
+
+namespace anib {
+
+struct Aev2Layout {
+  int off_r, off_rfc, off_s, off_a, off_afc, off_as, off_acc, off_f1, off_f2, off_p;   // forward
+  int off_d, off_j, off_adfc, off_ai, off_g;                                            // backward extras
+  int bytes;
+};
+
+template <typename T>
+__host__ __device__ inline Aev2Layout aev2_layout(int cap, int capA, int acc_elems, int nZ, int nA, bool backward) {
+  Aev2Layout L{};
+  int o = 0;
+  auto take = [&](int bytes, int align) { o = (o + align - 1) / align * align; int r = o; o += bytes; return r; };
+  const int ts = (int)sizeof(T);
+  L.off_a = take(capA * 4 * ts, 4 * ts);
+  if (backward) L.off_d = take(cap * 4 * ts, 4 * ts);
+  L.off_acc = take(acc_elems * ts, 16);
+  L.off_afc = take(capA * ts, 8);
+  L.off_as = take(capA * 4, 4);
+  if (!backward) {
+    L.off_r = take(cap * ts, 8);
+    L.off_rfc = take(cap * ts, 8);
+    L.off_f1 = take(32 * nZ * ts, 16);
+    L.off_f2 = take(32 * nA * ts, 16);
+    L.off_p = take(32 * 4, 4);
+  } else {
+    L.off_adfc = take(capA * ts, 8);
+    L.off_ai = take(capA * 4, 4);
+    L.off_g = take(cap * 3 * ts, 8);
+    L.off_j = take(cap * 4, 4);
+  }
+  L.off_s = take(cap * 4, 4);
+  L.bytes = (o + 31) / 32 * 32;
+  return L;
+}
+
+constexpr int kAev2Warps = 4;
+
+// ------------------------------------------------------------------------------------------------ forward
+template <typename T, int NZ, int NA>
+__global__ void __launch_bounds__(kAev2Warps * 32)
+aev2_forward_kernel(const __grid_constant__ AevConst<T> P, int radial_filter, const typename Vec4T<T>::type* __restrict__ x4,
+                    const int64_t* __restrict__ nbr_beg, const int* __restrict__ nbr_cnt, const int* __restrict__ jlist,
+                    const int* __restrict__ order, int nrows, T* __restrict__ aev, int64_t ld, void* __restrict__ aev_hi,
+                    void* __restrict__ aev_lo, int64_t ld_planes, int plane_mode, float plane_scale, int cap, int capA,
+                    int smem_per_warp, int* __restrict__ errflag) {
+  using V4 = typename Vec4T<T>::type;
+  extern __shared__ __align__(32) unsigned char smem_raw[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int row = blockIdx.x * kAev2Warps + warp;
+  if (row >= nrows) return;
+  const int nRpad = P.nR <= 16 ? 16 : 32;
+  const int npl = 32 / nRpad;
+  const int acc_elems = P.aev_len + (npl - 1) * P.rad_len;
+  const Aev2Layout L = aev2_layout<T>(cap, capA, acc_elems, NZ, NA, false);
+  unsigned char* base = smem_raw + (size_t)warp * smem_per_warp;
+  V4* sh_a = (V4*)(base + L.off_a);
+  T* acc = (T*)(base + L.off_acc);
+  T* sh_afc = (T*)(base + L.off_afc);
+  int* sh_as = (int*)(base + L.off_as);
+  T* sh_r = (T*)(base + L.off_r);
+  T* sh_rfc = (T*)(base + L.off_rfc);
+  T* sh_f1 = (T*)(base + L.off_f1);
+  T* sh_f2 = (T*)(base + L.off_f2);
+  int* sh_p = (int*)(base + L.off_p);
+  int* sh_s = (int*)(base + L.off_s);
+
+  const int i = order[row];
+  const V4 xi = x4[i];
+  const int* jl = jlist + nbr_beg[i];
+  const int cnt = nbr_cnt[i];
+  for (int t = lane; t < acc_elems; t += 32) acc[t] = T(0);
+  // ---- gather: coalesced list read, one vector load per neighbour, ballot compaction of the Rcr / Rca survivors
+  const unsigned lt = (1u << lane) - 1u;
+  int n = 0, na = 0;
+  for (int b0 = 0; b0 < cnt; b0 += 32) {
+    const int e = b0 + lane;
+    const bool valid = e < cnt;
+    const int j = valid ? __ldg(jl + e) : 0;
+    V4 p = xi;
+    if (valid) p = x4[j];
+    const T dx = p.x - xi.x, dy = p.y - xi.y, dz = p.z - xi.z;
+    const T r2 = dx * dx + dy * dy + dz * dz;
+    bool keep = valid && (!radial_filter || r2 <= P.Rcr2) && r2 > T(0);
+    const bool keepa = keep && r2 <= P.Rca2;
+    const unsigned m = __ballot_sync(0xffffffffu, keep);
+    const unsigned ma = __ballot_sync(0xffffffffu, keepa);
+    if (keep) {
+      const int pos = n + __popc(m & lt);
+      const T r = t_sqrt(r2);
+      sh_r[pos] = r;
+      sh_rfc[pos] = T(0.125) * t_cos(P.pi_over_Rcr * r) + T(0.125);   // 0.25 * fc(r; Rcr)
+      const int s = unpack_species(p.w);
+      sh_s[pos] = s;
+      if (keepa) {
+        const int posa = na + __popc(ma & lt);
+        if (posa < capA) {
+          const T inv = T(1) / r;
+          V4 u; u.x = dx * inv; u.y = dy * inv; u.z = dz * inv; u.w = r;
+          sh_a[posa] = u;
+          sh_afc[posa] = T(0.5) * t_cos(P.pi_over_Rca * r) + T(0.5);
+          sh_as[posa] = s;
+        }
+      }
+    }
+    n += __popc(m);
+    na += __popc(ma);
+  }
+  if (na > capA) { if (lane == 0) atomicExch(errflag, 1); na = capA; }
+  __syncwarp();
+
+  // ---- radial: lane = (sub-neighbour, shift k); the cutoff factor was computed once per neighbour in the gather
+  {
+    const int k = lane % nRpad, sub = lane / nRpad;
+    const T shf = P.ShfR[k < P.nR ? k : 0];
+    T* racc = (sub == 0) ? acc : acc + P.aev_len + (sub - 1) * P.rad_len;
+    for (int e0 = 0; e0 < n; e0 += npl) {
+      const int e = e0 + sub;
+      if (e < n && k < P.nR) {
+        const T dr = sh_r[e] - shf;
+        racc[sh_s[e] * P.nR + k] += sh_rfc[e] * t_exp(-P.EtaR * dr * dr);
+      }
+    }
+  }
+  // ---- angular: batches of 32 triples (row-major a < b)
+  {
+    const int ntri = na * (na - 1) / 2;
+    const int iz = lane % NZ, ia = lane / NZ;          // stage-2 role of this lane (lane < NA*NZ)
+    // stage-1 role: triple index -> (a, b), advanced incrementally
+    int ta = 0, rem = lane;
+    T accr = T(0);
+    int cur = -1;
+    T* aang = acc + P.rad_len + lane;
+    for (int t0 = 0; t0 < ntri; t0 += 32) {
+      if (t0 + lane < ntri) {
+        while (rem >= na - 1 - ta) { rem -= na - 1 - ta; ta++; }
+        const int a = ta, b = ta + 1 + rem;
+        const V4 A = sh_a[a], B = sh_a[b];
+        const T c = T(0.95) * (A.x * B.x + A.y * B.y + A.z * B.z);
+        const T sn = t_sqrt(fmax(T(0), T(1) - c * c));
+        const T fcp = T(2) * sh_afc[a] * sh_afc[b];
+#pragma unroll
+        for (int z = 0; z < NZ; z++) {
+          const T u = fmax(T(0), T(0.5) + T(0.5) * (c * P.cosZ[z] + sn * P.sinZ[z]));
+          sh_f1[lane * NZ + z] = fcp * t_pow(u, P.Zeta);
+        }
+        const T ravg = T(0.5) * (A.w + B.w);
+#pragma unroll
+        for (int q = 0; q < NA; q++) {
+          const T dr = ravg - P.ShfA[q];
+          sh_f2[lane * NA + q] = t_exp(-P.EtaA * dr * dr);
+        }
+        sh_p[lane] = P.triu[sh_as[a]][sh_as[b]];
+        rem += 32;
+      }
+      __syncwarp();
+      const int nb = min(32, ntri - t0);
+      if (lane < NA * NZ) {
+        for (int tt = 0; tt < nb; tt++) {
+          const int p = sh_p[tt];
+          if (p != cur) {                       // warp-uniform: every lane looks at the same triple
+            if (cur >= 0) aang[cur * (NA * NZ)] += accr;
+            cur = p; accr = T(0);
+          }
+          accr += sh_f1[tt * NZ + iz] * sh_f2[tt * NA + ia];
+        }
+      }
+      __syncwarp();
+    }
+    if (lane < NA * NZ && cur >= 0) aang[cur * (NA * NZ)] += accr;
+  }
+  __syncwarp();
+  // ---- one coalesced store of the row: fp32/fp64 row and / or operand planes for the tensor-core MLP
+  T* out = aev ? aev + (size_t)row * ld : nullptr;
+  if (plane_mode == 2 && out == nullptr && (P.aev_len & 1) == 0 && (P.rad_len & 1) == 0) {
+    __half2* ph = (__half2*)((__half*)aev_hi + (size_t)row * ld_planes);
+    __half2* pl = (__half2*)((__half*)aev_lo + (size_t)row * ld_planes);
+    for (int t = 2 * lane; t < P.aev_len; t += 64) {
+      float v0 = (float)acc[t], v1 = (float)acc[t + 1];
+      if (t < P.rad_len)
+        for (int s2 = 1; s2 < npl; s2++) {
+          v0 += (float)acc[P.aev_len + (s2 - 1) * P.rad_len + t];
+          v1 += (float)acc[P.aev_len + (s2 - 1) * P.rad_len + t + 1];
+        }
+      v0 *= plane_scale; v1 *= plane_scale;
+      const __half2 h = __floats2half2_rn(v0, v1);
+      const float2 hf = __half22float2(h);
+      ph[t >> 1] = h;
+      pl[t >> 1] = __floats2half2_rn(v0 - hf.x, v1 - hf.y);
+    }
+    return;
+  }
+  for (int t = lane; t < P.aev_len; t += 32) {
+    T v = acc[t];
+    if (t < P.rad_len)
+      for (int s2 = 1; s2 < npl; s2++) v += acc[P.aev_len + (s2 - 1) * P.rad_len + t];
+    if (out) out[t] = v;
+    if (plane_mode == 1) {
+      float f = (float)v;
+      float hi = round_tf32(f);
+      ((float*)aev_hi)[(size_t)row * ld_planes + t] = hi;
+      ((float*)aev_lo)[(size_t)row * ld_planes + t] = round_tf32(f - hi);
+    } else if (plane_mode == 2) {
+      const float f = (float)v * plane_scale;
+      const __half hi = __float2half_rn(f);
+      ((__half*)aev_hi)[(size_t)row * ld_planes + t] = hi;
+      ((__half*)aev_lo)[(size_t)row * ld_planes + t] = __float2half_rn(f - __half2float(hi));
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ backward
+// daev: dE/dAEV rows in bucket order (Hartree).  force: T[ntotal*3], accumulated with atomics (kcal/mol/A).
+// virial_slots: double[kVirialSlots*9], accumulated (kcal/mol), or nullptr.
+template <typename T, int NZ, int NA>
+__global__ void __launch_bounds__(kAev2Warps * 32)
+aev2_backward_kernel(const __grid_constant__ AevConst<T> P, int radial_filter, const typename Vec4T<T>::type* __restrict__ x4,
+                     const int64_t* __restrict__ nbr_beg, const int* __restrict__ nbr_cnt, const int* __restrict__ jlist,
+                     const int* __restrict__ order, int nrows, const T* __restrict__ daev, int64_t ld, T* __restrict__ force,
+                     double* __restrict__ virial_slots, T out_scale, int cap, int capA, int smem_per_warp) {
+  using V4 = typename Vec4T<T>::type;
+  extern __shared__ __align__(32) unsigned char smem_raw[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int row = blockIdx.x * kAev2Warps + warp;
+  if (row >= nrows) return;
+  const int rstride = P.nR + 1;            // padded rows: species / species pairs land in different banks
+  constexpr int astride = NA * NZ + 1;
+  const int acc_elems = P.S * rstride + P.npairs * astride;
+  const Aev2Layout L = aev2_layout<T>(cap, capA, acc_elems, NZ, NA, true);
+  unsigned char* base = smem_raw + (size_t)warp * smem_per_warp;
+  V4* sh_a = (V4*)(base + L.off_a);
+  V4* sh_d = (V4*)(base + L.off_d);
+  T* Arad = (T*)(base + L.off_acc);
+  T* Aang = Arad + P.S * rstride;
+  T* sh_afc = (T*)(base + L.off_afc);
+  T* sh_adfc = (T*)(base + L.off_adfc);
+  T* sh_g = (T*)(base + L.off_g);
+  int* sh_s = (int*)(base + L.off_s);
+  int* sh_j = (int*)(base + L.off_j);
+  int* sh_as = (int*)(base + L.off_as);
+  int* sh_ai = (int*)(base + L.off_ai);
+
+  const int i = order[row];
+  const V4 xi = x4[i];
+  const int* jl = jlist + nbr_beg[i];
+  const int cnt = nbr_cnt[i];
+  // upstream gradient row -> shared (coalesced read, padded rows)
+  const T* g_in = daev + (size_t)row * ld;
+  for (int t = lane; t < P.aev_len; t += 32) {
+    const T v = g_in[t];
+    if (t < P.rad_len) Arad[(t / P.nR) * rstride + (t % P.nR)] = v;
+    else { const int q = t - P.rad_len; Aang[(q / (NA * NZ)) * astride + (q % (NA * NZ))] = v; }
+  }
+  // ---- gather (as in the forward pass, plus what the gradients need)
+  const unsigned lt = (1u << lane) - 1u;
+  int n = 0, na = 0;
+  for (int b0 = 0; b0 < cnt; b0 += 32) {
+    const int e = b0 + lane;
+    const bool valid = e < cnt;
+    const int j = valid ? __ldg(jl + e) : 0;
+    V4 p = xi;
+    if (valid) p = x4[j];
+    const T dx = p.x - xi.x, dy = p.y - xi.y, dz = p.z - xi.z;
+    const T r2 = dx * dx + dy * dy + dz * dz;
+    const bool keep = valid && (!radial_filter || r2 <= P.Rcr2) && r2 > T(0);
+    const bool keepa = keep && r2 <= P.Rca2;
+    const unsigned m = __ballot_sync(0xffffffffu, keep);
+    const unsigned ma = __ballot_sync(0xffffffffu, keepa);
+    if (keep) {
+      const int pos = n + __popc(m & lt);
+      const T r = t_sqrt(r2);
+      V4 d; d.x = dx; d.y = dy; d.z = dz; d.w = r;
+      sh_d[pos] = d;
+      const int s = unpack_species(p.w);
+      sh_s[pos] = s;
+      sh_j[pos] = j;
+      if (keepa) {
+        const int posa = na + __popc(ma & lt);
+        if (posa < capA) {
+          const T inv = T(1) / r;
+          V4 u; u.x = dx * inv; u.y = dy * inv; u.z = dz * inv; u.w = r;
+          sh_a[posa] = u;
+          T sn, cs;
+          t_sincos(P.pi_over_Rca * r, &sn, &cs);
+          sh_afc[posa] = T(0.5) * cs + T(0.5);
+          sh_adfc[posa] = T(-0.5) * P.pi_over_Rca * sn;
+          sh_as[posa] = s;
+          sh_ai[posa] = pos;
+        }
+      }
+    }
+    n += __popc(m);
+    na += __popc(ma);
+  }
+  if (na > capA) na = capA;   // the forward pass raised the error flag
+  __syncwarp();
+
+  // ---- radial: lane = neighbour
+  for (int e = lane; e < n; e += 32) {
+    const V4 d = sh_d[e];
+    const T r = d.w;
+    T sn, cs;
+    t_sincos(P.pi_over_Rcr * r, &sn, &cs);
+    const T fc = T(0.5) * cs + T(0.5), dfc = T(-0.5) * P.pi_over_Rcr * sn;
+    const T* Ar = Arad + sh_s[e] * rstride;
+    T acc = T(0);
+    for (int k = 0; k < P.nR; k++) {
+      const T dr = r - P.ShfR[k];
+      acc += Ar[k] * t_exp(-P.EtaR * dr * dr) * (dfc - T(2) * P.EtaR * dr * fc);
+    }
+    const T coef = T(0.25) * acc / r;
+    sh_g[3 * e + 0] = coef * d.x; sh_g[3 * e + 1] = coef * d.y; sh_g[3 * e + 2] = coef * d.z;
+  }
+  __syncwarp();
+  // ---- angular: lane = triple, enumerated along wrapped diagonals (a, (a+k) mod na), k = 1 .. na/2
+  {
+    const int ntri = na * (na - 1) / 2;
+    const int nfull = na * ((na - 1) / 2);        // triples on the complete diagonals (all of them when na is odd)
+    for (int t = lane; t < ntri; t += 32) {
+      int a, b;
+      if (t < nfull) { const int k = t / na; a = t - k * na; b = a + k + 1; if (b >= na) b -= na; }
+      else { a = t - nfull; b = a + na / 2; }
+      const V4 A = sh_a[a], B = sh_a[b];
+      const T fca = sh_afc[a], fcb = sh_afc[b];
+      const T cosv = A.x * B.x + A.y * B.y + A.z * B.z;
+      const T c = T(0.95) * cosv;
+      const T sn = t_sqrt(fmax(T(0), T(1) - c * c));
+      const T c_over_sn = c / sn;
+      T f1[NZ], df1[NZ];
+#pragma unroll
+      for (int z = 0; z < NZ; z++) {
+        const T u = fmax(T(0), T(0.5) + T(0.5) * (c * P.cosZ[z] + sn * P.sinZ[z]));
+        const T um1 = t_pow(u, P.Zeta - T(1));
+        f1[z] = um1 * u;
+        df1[z] = P.Zeta * um1 * T(0.5) * (P.cosZ[z] - c_over_sn * P.sinZ[z]);   // d f1 / d c
+      }
+      const T ravg = T(0.5) * (A.w + B.w);
+      const T* w = Aang + P.triu[sh_as[a]][sh_as[b]] * astride;
+      T S0 = T(0), S1 = T(0), S2 = T(0);
+#pragma unroll
+      for (int q = 0; q < NA; q++) {
+        const T dr = ravg - P.ShfA[q];
+        const T f2 = t_exp(-P.EtaA * dr * dr);
+        const T df2 = T(-2) * P.EtaA * dr * f2;
+        T Pz = T(0), Qz = T(0);
+#pragma unroll
+        for (int z = 0; z < NZ; z++) {
+          const T wv = w[q * NZ + z];
+          Pz += wv * f1[z];
+          Qz += wv * df1[z];
+        }
+        S0 += Pz * f2; S1 += Pz * df2; S2 += Qz * f2;
+      }
+      const T half_s1 = fca * fcb * S1;                                  // 2 * fca fcb * 0.5 * S1
+      const T dE_dra = T(2) * sh_adfc[a] * fcb * S0 + half_s1;
+      const T dE_drb = T(2) * fca * sh_adfc[b] * S0 + half_s1;
+      const T dE_dcos = T(2) * fca * fcb * T(0.95) * S2;
+      const T ka = dE_dcos / A.w, kb = dE_dcos / B.w;
+      const int ea = sh_ai[a], eb = sh_ai[b];
+      atomicAdd(sh_g + 3 * ea + 0, dE_dra * A.x + ka * (B.x - cosv * A.x));
+      atomicAdd(sh_g + 3 * ea + 1, dE_dra * A.y + ka * (B.y - cosv * A.y));
+      atomicAdd(sh_g + 3 * ea + 2, dE_dra * A.z + ka * (B.z - cosv * A.z));
+      atomicAdd(sh_g + 3 * eb + 0, dE_drb * B.x + kb * (A.x - cosv * B.x));
+      atomicAdd(sh_g + 3 * eb + 1, dE_drb * B.y + kb * (A.y - cosv * B.y));
+      atomicAdd(sh_g + 3 * eb + 2, dE_drb * B.z + kb * (A.z - cosv * B.z));
+    }
+  }
+  __syncwarp();
+  // ---- scatter: F_j -= g, F_i += sum g, virial -= g (x) d
+  T fix = T(0), fiy = T(0), fiz = T(0);
+  double vir[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+  for (int e = lane; e < n; e += 32) {
+    const T gx = sh_g[3 * e + 0] * out_scale, gy = sh_g[3 * e + 1] * out_scale, gz = sh_g[3 * e + 2] * out_scale;
+    const int j = sh_j[e];
+    atomic_add_t(force + 3 * (size_t)j + 0, -gx);
+    atomic_add_t(force + 3 * (size_t)j + 1, -gy);
+    atomic_add_t(force + 3 * (size_t)j + 2, -gz);
+    fix += gx; fiy += gy; fiz += gz;
+    if (virial_slots != nullptr) {
+      const V4 d = sh_d[e];
+      vir[0] -= (double)(gx * d.x); vir[1] -= (double)(gx * d.y); vir[2] -= (double)(gx * d.z);
+      vir[3] -= (double)(gy * d.x); vir[4] -= (double)(gy * d.y); vir[5] -= (double)(gy * d.z);
+      vir[6] -= (double)(gz * d.x); vir[7] -= (double)(gz * d.y); vir[8] -= (double)(gz * d.z);
+    }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    fix += __shfl_xor_sync(0xffffffffu, fix, o);
+    fiy += __shfl_xor_sync(0xffffffffu, fiy, o);
+    fiz += __shfl_xor_sync(0xffffffffu, fiz, o);
+  }
+  if (lane == 0) {
+    atomic_add_t(force + 3 * (size_t)i + 0, fix);
+    atomic_add_t(force + 3 * (size_t)i + 1, fiy);
+    atomic_add_t(force + 3 * (size_t)i + 2, fiz);
+  }
+  if (virial_slots != nullptr) {
+#pragma unroll
+    for (int q = 0; q < 9; q++) {
+      double v = vir[q];
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+      if (lane == 0) atomicAdd(virial_slots + (size_t)(blockIdx.x % kVirialSlots) * 9 + q, v);
+    }
+  }
+}
+
+}  // namespace anib

@@ -13,6 +13,7 @@
 
 #include "../../include/ani_b200.h"
 #include "aev.cuh"
+#include "aev2.cuh"
 #include "common.cuh"
 #include "misc.cuh"
 #include "mlp_simt.cuh"
@@ -136,7 +137,9 @@ struct Engine : EngineBase {
   int64_t ld_aev = 0;
   int chunk_rows = 2048;
 
+  int aev_gen = 2;   // 2: triple-per-lane kernels (aev2.cuh); 1: the first-generation kernels (aev.cuh), env ANI_B200_AEV=1
   Engine(ani_ctx* ctx, const HostModel& m, int M_) : c(ctx), hm(m), M(M_) {
+    if (const char* g = getenv("ANI_B200_AEV")) aev_gen = atoi(g) == 1 ? 1 : 2;
     const char* e = getenv("ANI_B200_MLP_CHUNK");
     if (e && atoi(e) > 0) chunk_rows = atoi(e);
   }
@@ -367,10 +370,25 @@ struct Engine : EngineBase {
         ANIB_RESERVE(d_aev_lo, (size_t)tc_padded_rows(nlocal, hm.S) * ld_aev * sizeof(float));
         hi = d_aev_hi.p; lo = d_aev_lo.p; plane_mode = 1;
       }
-      aev_forward_kernel<T><<<(nlocal + kAevWarps - 1) / kAevWarps, kAevWarps * 32, smem, st>>>(
-          P, c->use_cuaev ? 1 : 0, d_x4.as<V4>(), d_beg.as<int64_t>(), d_cnt.as<int>(), d_jlist.as<int>(),
-          d_order.as<int>(), nlocal, rows, ld_aev, hi, lo, ldp, plane_mode, f16::kScaleAev, cap, capA, Lf.bytes,
-          d_err.as<int>());
+      auto launch2 = [&](auto kern) -> int {
+        const Aev2Layout L2 = aev2_layout<T>(cap, capA, acc_f, P.nZ, P.nA, false);
+        const int smem2 = L2.bytes * kAev2Warps;
+        ANIB_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem2));
+        kern<<<(nlocal + kAev2Warps - 1) / kAev2Warps, kAev2Warps * 32, smem2, st>>>(
+            P, c->use_cuaev ? 1 : 0, d_x4.as<V4>(), d_beg.as<int64_t>(), d_cnt.as<int>(), d_jlist.as<int>(), d_order.as<int>(),
+            nlocal, rows, ld_aev, hi, lo, ldp, plane_mode, f16::kScaleAev, cap, capA, L2.bytes, d_err.as<int>());
+        return 0;
+      };
+      int rc2 = 0;
+      if (aev_gen == 2 && P.nZ == 4 && P.nA == 8) rc2 = launch2(aev2_forward_kernel<T, 4, 8>);
+      else if (aev_gen == 2 && P.nZ == 8 && P.nA == 4) rc2 = launch2(aev2_forward_kernel<T, 8, 4>);
+      else if (aev_gen == 2 && P.nZ == 8 && P.nA == 8) rc2 = launch2(aev2_forward_kernel<T, 8, 8>);
+      else
+        aev_forward_kernel<T><<<(nlocal + kAevWarps - 1) / kAevWarps, kAevWarps * 32, smem, st>>>(
+            P, c->use_cuaev ? 1 : 0, d_x4.as<V4>(), d_beg.as<int64_t>(), d_cnt.as<int>(), d_jlist.as<int>(),
+            d_order.as<int>(), nlocal, rows, ld_aev, hi, lo, ldp, plane_mode, f16::kScaleAev, cap, capA, Lf.bytes,
+            d_err.as<int>());
+      if (rc2) return rc2;
       c->launches++;
     }
     if (tm) cudaEventRecord(c->ev[2], st);
@@ -396,8 +414,22 @@ struct Engine : EngineBase {
         c->launches++;
         return 0;
       };
+      auto launch2 = [&](auto kern) -> int {
+        const Aev2Layout L2 = aev2_layout<T>(cap, capA, acc_b, P.nZ, P.nA, true);
+        const int smem2 = L2.bytes * kAev2Warps;
+        ANIB_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem2));
+        kern<<<(nlocal + kAev2Warps - 1) / kAev2Warps, kAev2Warps * 32, smem2, st>>>(
+            P, c->use_cuaev ? 1 : 0, d_x4.as<V4>(), d_beg.as<int64_t>(), d_cnt.as<int>(), d_jlist.as<int>(), d_order.as<int>(),
+            nlocal, d_daev.as<T>(), ld_aev, d_force.as<T>(), want_virial ? d_virial.as<double>() : nullptr,
+            (T)kHartree2KcalMol, cap, capA, L2.bytes);
+        c->launches++;
+        return 0;
+      };
       int rc;
-      if (P.nZ == 4) rc = launch(aev_backward_kernel<T, 4>);
+      if (aev_gen == 2 && P.nZ == 4 && P.nA == 8) rc = launch2(aev2_backward_kernel<T, 4, 8>);
+      else if (aev_gen == 2 && P.nZ == 8 && P.nA == 4) rc = launch2(aev2_backward_kernel<T, 8, 4>);
+      else if (aev_gen == 2 && P.nZ == 8 && P.nA == 8) rc = launch2(aev2_backward_kernel<T, 8, 8>);
+      else if (P.nZ == 4) rc = launch(aev_backward_kernel<T, 4>);
       else if (P.nZ == 8) rc = launch(aev_backward_kernel<T, 8>);
       else if (P.nZ == 1) rc = launch(aev_backward_kernel<T, 1>);
       else if (P.nZ == 2) rc = launch(aev_backward_kernel<T, 2>);
