@@ -18,11 +18,13 @@
 namespace anib {
 
 struct Aev2Layout {
-  int off_r, off_rfc, off_s, off_a, off_afc, off_as, off_acc, off_f1, off_f2, off_p;   // forward
-  int off_d, off_j, off_adfc, off_ai, off_g;                                            // backward extras
+  int off_r, off_rfc, off_s, off_a, off_afc, off_as, off_acc, off_f1, off_f2, off_ud, off_us, off_seg;   // forward
+  int off_d, off_j, off_adfc, off_ai, off_g;                                                              // backward extras
   int bytes;
 };
 
+// Forward: unsorted gather buffers (ud, us) -> species-sorted radial (r, rfc) and angular (a, afc) lists; the triple
+// batch buffers f1 / f2 alias the unsorted buffer, which is dead once the lists are sorted.
 template <typename T>
 __host__ __device__ inline Aev2Layout aev2_layout(int cap, int capA, int acc_elems, int nZ, int nA, bool backward) {
   Aev2Layout L{};
@@ -31,22 +33,27 @@ __host__ __device__ inline Aev2Layout aev2_layout(int cap, int capA, int acc_ele
   const int ts = (int)sizeof(T);
   L.off_a = take(capA * 4 * ts, 4 * ts);
   if (backward) L.off_d = take(cap * 4 * ts, 4 * ts);
+  else {
+    const int ud = cap * 4 * ts, fb = 32 * (nZ + nA) * ts;
+    L.off_ud = take(ud > fb ? ud : fb, 4 * ts);
+    L.off_f1 = L.off_ud;
+    L.off_f2 = L.off_ud + 32 * nZ * ts;
+  }
   L.off_acc = take(acc_elems * ts, 16);
   L.off_afc = take(capA * ts, 8);
-  L.off_as = take(capA * 4, 4);
   if (!backward) {
     L.off_r = take(cap * ts, 8);
     L.off_rfc = take(cap * ts, 8);
-    L.off_f1 = take(32 * nZ * ts, 16);
-    L.off_f2 = take(32 * nA * ts, 16);
-    L.off_p = take(32 * 4, 4);
+    L.off_us = take(cap * 4, 4);
+    L.off_seg = take(4 * (kMaxSpecies + 1) * 4, 4);   // roff, aoff, run_r, run_a
   } else {
+    L.off_as = take(capA * 4, 4);
     L.off_adfc = take(capA * ts, 8);
     L.off_ai = take(capA * 4, 4);
     L.off_g = take(cap * 3 * ts, 8);
     L.off_j = take(cap * 4, 4);
+    L.off_s = take(cap * 4, 4);
   }
-  L.off_s = take(cap * 4, 4);
   L.bytes = (o + 31) / 32 * 32;
   return L;
 }
@@ -66,140 +73,196 @@ aev2_forward_kernel(const __grid_constant__ AevConst<T> P, int radial_filter, co
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int row = blockIdx.x * kAev2Warps + warp;
   if (row >= nrows) return;
-  const int nRpad = P.nR <= 16 ? 16 : 32;
-  const int npl = 32 / nRpad;
-  const int acc_elems = P.aev_len + (npl - 1) * P.rad_len;
-  const Aev2Layout L = aev2_layout<T>(cap, capA, acc_elems, NZ, NA, false);
+  const Aev2Layout L = aev2_layout<T>(cap, capA, P.aev_len, NZ, NA, false);
   unsigned char* base = smem_raw + (size_t)warp * smem_per_warp;
   V4* sh_a = (V4*)(base + L.off_a);
+  V4* sh_ud = (V4*)(base + L.off_ud);
   T* acc = (T*)(base + L.off_acc);
   T* sh_afc = (T*)(base + L.off_afc);
-  int* sh_as = (int*)(base + L.off_as);
   T* sh_r = (T*)(base + L.off_r);
   T* sh_rfc = (T*)(base + L.off_rfc);
   T* sh_f1 = (T*)(base + L.off_f1);
   T* sh_f2 = (T*)(base + L.off_f2);
-  int* sh_p = (int*)(base + L.off_p);
-  int* sh_s = (int*)(base + L.off_s);
+  int* sh_us = (int*)(base + L.off_us);
+  int* roff = (int*)(base + L.off_seg);            // [S+1] start of each species' segment in the radial list
+  int* aoff = roff + (kMaxSpecies + 1);            // [S+1] same for the angular list
+  int* run_r = aoff + (kMaxSpecies + 1);
+  int* run_a = run_r + (kMaxSpecies + 1);
 
   const int i = order[row];
   const V4 xi = x4[i];
   const int* jl = jlist + nbr_beg[i];
   const int cnt = nbr_cnt[i];
-  for (int t = lane; t < acc_elems; t += 32) acc[t] = T(0);
-  // ---- gather: coalesced list read, one vector load per neighbour, ballot compaction of the Rcr / Rca survivors
+  for (int t = lane; t < P.aev_len; t += 32) acc[t] = T(0);
+  if (lane <= kMaxSpecies) { run_r[lane] = 0; run_a[lane] = 0; }
+  __syncwarp();
+  // ---- gather: coalesced list read, one vector load per neighbour, ballot compaction of the Rcr survivors (unsorted),
+  //      per-species counts of the radial / angular survivors (one leader lane per species present in the chunk)
   const unsigned lt = (1u << lane) - 1u;
   int n = 0, na = 0;
+  int jn = lane < cnt ? __ldg(jl + lane) : 0;
   for (int b0 = 0; b0 < cnt; b0 += 32) {
     const int e = b0 + lane;
     const bool valid = e < cnt;
-    const int j = valid ? __ldg(jl + e) : 0;
+    const int j = jn;
+    if (e + 32 < cnt) jn = __ldg(jl + e + 32);      // next chunk's indices are in flight while this chunk is processed
     V4 p = xi;
     if (valid) p = x4[j];
     const T dx = p.x - xi.x, dy = p.y - xi.y, dz = p.z - xi.z;
     const T r2 = dx * dx + dy * dy + dz * dz;
-    bool keep = valid && (!radial_filter || r2 <= P.Rcr2) && r2 > T(0);
+    const bool keep = valid && (!radial_filter || r2 <= P.Rcr2) && r2 > T(0);
     const bool keepa = keep && r2 <= P.Rca2;
     const unsigned m = __ballot_sync(0xffffffffu, keep);
     const unsigned ma = __ballot_sync(0xffffffffu, keepa);
     if (keep) {
       const int pos = n + __popc(m & lt);
-      const T r = t_sqrt(r2);
-      sh_r[pos] = r;
-      sh_rfc[pos] = T(0.125) * t_cos(P.pi_over_Rcr * r) + T(0.125);   // 0.25 * fc(r; Rcr)
       const int s = unpack_species(p.w);
-      sh_s[pos] = s;
+      V4 d; d.x = dx; d.y = dy; d.z = dz; d.w = t_sqrt(r2);
+      sh_ud[pos] = d;
+      sh_us[pos] = s | (keepa ? 256 : 0);
+      const unsigned grp = __match_any_sync(m, s);
+      if ((grp & lt) == 0) run_r[s] += __popc(grp);
       if (keepa) {
-        const int posa = na + __popc(ma & lt);
-        if (posa < capA) {
-          const T inv = T(1) / r;
-          V4 u; u.x = dx * inv; u.y = dy * inv; u.z = dz * inv; u.w = r;
-          sh_a[posa] = u;
-          sh_afc[posa] = T(0.5) * t_cos(P.pi_over_Rca * r) + T(0.5);
-          sh_as[posa] = s;
-        }
+        const unsigned ga = grp & ma;
+        if ((ga & lt) == 0) run_a[s] += __popc(ga);
       }
     }
+    __syncwarp();
     n += __popc(m);
     na += __popc(ma);
   }
-  if (na > capA) { if (lane == 0) atomicExch(errflag, 1); na = capA; }
+  if (na > capA) { if (lane == 0) atomicExch(errflag, 1); }
+  // ---- segment offsets (exclusive prefix over species), run counters reset
+  if (lane == 0) {
+    int o_r = 0, o_a = 0;
+    for (int s = 0; s < P.S; s++) {
+      const int cr = run_r[s], ca = run_a[s];
+      roff[s] = o_r; aoff[s] = o_a; run_r[s] = 0; run_a[s] = 0;
+      o_r += cr; o_a += ca;
+    }
+    roff[P.S] = o_r; aoff[P.S] = o_a;
+  }
   __syncwarp();
+  // ---- scatter into species-sorted lists; cutoff factors are computed once per neighbour here
+  for (int b0 = 0; b0 < n; b0 += 32) {
+    const int e = b0 + lane;
+    const bool valid = e < n;
+    V4 d = xi; int s = 0;
+    bool isa = false;
+    if (valid) { d = sh_ud[e]; const int us = sh_us[e]; s = us & 255; isa = (us & 256) != 0; }
+    const unsigned m = __ballot_sync(0xffffffffu, valid);
+    const unsigned ma = __ballot_sync(0xffffffffu, isa);
+    if (valid) {
+      const unsigned grp = __match_any_sync(m, s);
+      const int pos = roff[s] + run_r[s] + __popc(grp & lt);
+      const unsigned ga = grp & ma;
+      const int posa = aoff[s] + run_a[s] + __popc(ga & lt);
+      __syncwarp(m);
+      if ((grp & lt) == 0) run_r[s] += __popc(grp);
+      if (isa && (ga & lt) == 0) run_a[s] += __popc(ga);
+      const T r = d.w;
+      sh_r[pos] = r;
+      sh_rfc[pos] = T(0.125) * t_cos(P.pi_over_Rcr * r) + T(0.125);   // 0.25 * fc(r; Rcr)
+      if (isa && posa < capA) {
+        const T inv = T(1) / r;
+        V4 u; u.x = d.x * inv; u.y = d.y * inv; u.z = d.z * inv; u.w = r;
+        sh_a[posa] = u;
+        sh_afc[posa] = T(0.5) * t_cos(P.pi_over_Rca * r) + T(0.5);
+      }
+    }
+    __syncwarp();
+  }
 
-  // ---- radial: lane = (sub-neighbour, shift k); the cutoff factor was computed once per neighbour in the gather
+  // ---- radial: lane = (sub-neighbour, shift k); one species segment at a time, accumulated in a register
   {
+    const int nRpad = P.nR <= 16 ? 16 : 32;
+    const int npl = 32 / nRpad;
     const int k = lane % nRpad, sub = lane / nRpad;
     const T shf = P.ShfR[k < P.nR ? k : 0];
-    T* racc = (sub == 0) ? acc : acc + P.aev_len + (sub - 1) * P.rad_len;
-    for (int e0 = 0; e0 < n; e0 += npl) {
-      const int e = e0 + sub;
-      if (e < n && k < P.nR) {
+    for (int s = 0; s < P.S; s++) {
+      const int e1 = roff[s + 1];
+      if (roff[s] == e1) continue;
+      T accr = T(0);
+      for (int e = roff[s] + sub; e < e1; e += npl) {
         const T dr = sh_r[e] - shf;
-        racc[sh_s[e] * P.nR + k] += sh_rfc[e] * t_exp(-P.EtaR * dr * dr);
+        accr += sh_rfc[e] * t_exp(-P.EtaR * dr * dr);
       }
+      if (npl == 2) accr += __shfl_xor_sync(0xffffffffu, accr, 16);
+      if (lane < P.nR) acc[s * P.nR + lane] = accr;
     }
   }
-  // ---- angular: batches of 32 triples (row-major a < b)
+  // ---- angular: one species pair (s <= t) at a time; batches of 32 triples: stage 1 lane = triple, stage 2 lane = term
   {
-    const int ntri = na * (na - 1) / 2;
-    const int iz = lane % NZ, ia = lane / NZ;          // stage-2 role of this lane (lane < NA*NZ)
-    // stage-1 role: triple index -> (a, b), advanced incrementally
-    int ta = 0, rem = lane;
-    T accr = T(0);
-    int cur = -1;
-    T* aang = acc + P.rad_len + lane;
-    for (int t0 = 0; t0 < ntri; t0 += 32) {
-      if (t0 + lane < ntri) {
-        while (rem >= na - 1 - ta) { rem -= na - 1 - ta; ta++; }
-        const int a = ta, b = ta + 1 + rem;
-        const V4 A = sh_a[a], B = sh_a[b];
-        const T c = T(0.95) * (A.x * B.x + A.y * B.y + A.z * B.z);
-        const T sn = t_sqrt(fmax(T(0), T(1) - c * c));
-        const T fcp = T(2) * sh_afc[a] * sh_afc[b];
+    const int iz = lane % NZ, ia = lane / NZ;
+    for (int s = 0; s < P.S; s++) {
+      const int as0 = min(aoff[s], capA), ns = min(aoff[s + 1], capA) - as0;
+      if (ns == 0) continue;
+      for (int t = s; t < P.S; t++) {
+        const int at0 = min(aoff[t], capA), nt = min(aoff[t + 1], capA) - at0;
+        const int ntri = (s == t) ? ns * (ns - 1) / 2 : ns * nt;
+        if (ntri == 0) continue;
+        T accr = T(0);
+        int ta = 0, rem = lane;                       // triangular enumeration state (s == t)
+        for (int t0 = 0; t0 < ntri; t0 += 32) {
+          const int idx = t0 + lane;
+          if (idx < ntri) {
+            int a, b;
+            if (s == t) {
+              while (rem >= ns - 1 - ta) { rem -= ns - 1 - ta; ta++; }
+              a = as0 + ta; b = a + 1 + rem;
+              rem += 32;
+            } else {
+              const int qa = idx / nt;
+              a = as0 + qa; b = at0 + (idx - qa * nt);
+            }
+            const V4 A = sh_a[a], B = sh_a[b];
+            const T c = T(0.95) * (A.x * B.x + A.y * B.y + A.z * B.z);
+            const T sn = t_sqrt(fmax(T(0), T(1) - c * c));
+            const T fcp = T(2) * sh_afc[a] * sh_afc[b];
+            T f1[NZ], f2[NA];
 #pragma unroll
-        for (int z = 0; z < NZ; z++) {
-          const T u = fmax(T(0), T(0.5) + T(0.5) * (c * P.cosZ[z] + sn * P.sinZ[z]));
-          sh_f1[lane * NZ + z] = fcp * t_pow(u, P.Zeta);
-        }
-        const T ravg = T(0.5) * (A.w + B.w);
+            for (int z = 0; z < NZ; z++) {
+              const T u = fmax(T(0), T(0.5) + T(0.5) * (c * P.cosZ[z] + sn * P.sinZ[z]));
+              f1[z] = fcp * t_pow(u, P.Zeta);
+            }
+            const T ravg = T(0.5) * (A.w + B.w);
 #pragma unroll
-        for (int q = 0; q < NA; q++) {
-          const T dr = ravg - P.ShfA[q];
-          sh_f2[lane * NA + q] = t_exp(-P.EtaA * dr * dr);
-        }
-        sh_p[lane] = P.triu[sh_as[a]][sh_as[b]];
-        rem += 32;
-      }
-      __syncwarp();
-      const int nb = min(32, ntri - t0);
-      if (lane < NA * NZ) {
-        for (int tt = 0; tt < nb; tt++) {
-          const int p = sh_p[tt];
-          if (p != cur) {                       // warp-uniform: every lane looks at the same triple
-            if (cur >= 0) aang[cur * (NA * NZ)] += accr;
-            cur = p; accr = T(0);
+            for (int q = 0; q < NA; q++) {
+              const T dr = ravg - P.ShfA[q];
+              f2[q] = t_exp(-P.EtaA * dr * dr);
+            }
+            if (NZ % 4 == 0 && NA % 4 == 0) {        // vector stores: no bank conflicts
+#pragma unroll
+              for (int z = 0; z < NZ; z += 4) { V4 v; v.x = f1[z]; v.y = f1[z + 1]; v.z = f1[z + 2]; v.w = f1[z + 3]; *(V4*)(sh_f1 + lane * NZ + z) = v; }
+#pragma unroll
+              for (int q = 0; q < NA; q += 4) { V4 v; v.x = f2[q]; v.y = f2[q + 1]; v.z = f2[q + 2]; v.w = f2[q + 3]; *(V4*)(sh_f2 + lane * NA + q) = v; }
+            } else {
+#pragma unroll
+              for (int z = 0; z < NZ; z++) sh_f1[lane * NZ + z] = f1[z];
+#pragma unroll
+              for (int q = 0; q < NA; q++) sh_f2[lane * NA + q] = f2[q];
+            }
           }
-          accr += sh_f1[tt * NZ + iz] * sh_f2[tt * NA + ia];
+          __syncwarp();
+          const int nb = min(32, ntri - t0);
+          if (lane < NA * NZ) {
+#pragma unroll 4
+            for (int tt = 0; tt < nb; tt++) accr += sh_f1[tt * NZ + iz] * sh_f2[tt * NA + ia];
+          }
+          __syncwarp();
         }
+        if (lane < NA * NZ) acc[P.rad_len + P.triu[s][t] * (NA * NZ) + lane] = accr;
       }
-      __syncwarp();
     }
-    if (lane < NA * NZ && cur >= 0) aang[cur * (NA * NZ)] += accr;
   }
   __syncwarp();
   // ---- one coalesced store of the row: fp32/fp64 row and / or operand planes for the tensor-core MLP
   T* out = aev ? aev + (size_t)row * ld : nullptr;
-  if (plane_mode == 2 && out == nullptr && (P.aev_len & 1) == 0 && (P.rad_len & 1) == 0) {
+  if (plane_mode == 2 && out == nullptr && (P.aev_len & 1) == 0) {
     __half2* ph = (__half2*)((__half*)aev_hi + (size_t)row * ld_planes);
     __half2* pl = (__half2*)((__half*)aev_lo + (size_t)row * ld_planes);
     for (int t = 2 * lane; t < P.aev_len; t += 64) {
-      float v0 = (float)acc[t], v1 = (float)acc[t + 1];
-      if (t < P.rad_len)
-        for (int s2 = 1; s2 < npl; s2++) {
-          v0 += (float)acc[P.aev_len + (s2 - 1) * P.rad_len + t];
-          v1 += (float)acc[P.aev_len + (s2 - 1) * P.rad_len + t + 1];
-        }
-      v0 *= plane_scale; v1 *= plane_scale;
+      const float v0 = (float)acc[t] * plane_scale, v1 = (float)acc[t + 1] * plane_scale;
       const __half2 h = __floats2half2_rn(v0, v1);
       const float2 hf = __half22float2(h);
       ph[t >> 1] = h;
@@ -208,9 +271,7 @@ aev2_forward_kernel(const __grid_constant__ AevConst<T> P, int radial_filter, co
     return;
   }
   for (int t = lane; t < P.aev_len; t += 32) {
-    T v = acc[t];
-    if (t < P.rad_len)
-      for (int s2 = 1; s2 < npl; s2++) v += acc[P.aev_len + (s2 - 1) * P.rad_len + t];
+    const T v = acc[t];
     if (out) out[t] = v;
     if (plane_mode == 1) {
       float f = (float)v;
@@ -261,12 +322,26 @@ aev2_backward_kernel(const __grid_constant__ AevConst<T> P, int radial_filter, c
   const V4 xi = x4[i];
   const int* jl = jlist + nbr_beg[i];
   const int cnt = nbr_cnt[i];
-  // upstream gradient row -> shared (coalesced read, padded rows)
-  const T* g_in = daev + (size_t)row * ld;
-  for (int t = lane; t < P.aev_len; t += 32) {
-    const T v = g_in[t];
-    if (t < P.rad_len) Arad[(t / P.nR) * rstride + (t % P.nR)] = v;
-    else { const int q = t - P.rad_len; Aang[(q / (NA * NZ)) * astride + (q % (NA * NZ))] = v; }
+  // upstream gradient row -> shared, asynchronously (cp.async, 4/8-byte elements into the padded rows): the copy is in flight
+  // while the neighbour list is gathered below
+  {
+    const T* g_in = daev + (size_t)row * ld;
+    const bool pow2 = (P.nR & (P.nR - 1)) == 0;
+    const int sh = 31 - __clz(P.nR);
+    for (int t = lane; t < P.aev_len; t += 32) {
+      T* dst;
+      if (t < P.rad_len) {
+        const int s = pow2 ? (t >> sh) : (t / P.nR);
+        dst = Arad + s * rstride + (t - s * P.nR);
+      } else {
+        const int q = t - P.rad_len;
+        dst = Aang + (q / (NA * NZ)) * astride + (q % (NA * NZ));
+      }
+      const uint32_t d32 = (uint32_t)__cvta_generic_to_shared(dst);
+      if (sizeof(T) == 4) asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d32), "l"(g_in + t) : "memory");
+      else asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(d32), "l"(g_in + t) : "memory");
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
   }
   // ---- gather (as in the forward pass, plus what the gradients need)
   const unsigned lt = (1u << lane) - 1u;
@@ -310,6 +385,7 @@ aev2_backward_kernel(const __grid_constant__ AevConst<T> P, int radial_filter, c
     na += __popc(ma);
   }
   if (na > capA) na = capA;   // the forward pass raised the error flag
+  asm volatile("cp.async.wait_all;" ::: "memory");
   __syncwarp();
 
   // ---- radial: lane = neighbour

@@ -371,7 +371,7 @@ struct Engine : EngineBase {
         hi = d_aev_hi.p; lo = d_aev_lo.p; plane_mode = 1;
       }
       auto launch2 = [&](auto kern) -> int {
-        const Aev2Layout L2 = aev2_layout<T>(cap, capA, acc_f, P.nZ, P.nA, false);
+        const Aev2Layout L2 = aev2_layout<T>(cap, capA, P.aev_len, P.nZ, P.nA, false);
         const int smem2 = L2.bytes * kAev2Warps;
         ANIB_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem2));
         kern<<<(nlocal + kAev2Warps - 1) / kAev2Warps, kAev2Warps * 32, smem2, st>>>(
