@@ -159,7 +159,7 @@ struct Engine : EngineBase {
     for (int s = 0; s < hm.S; s++)
       for (int t = s; t < hm.S; t++) { P.triu[s][t] = p; P.triu[t][s] = p; p++; }
     ld_aev = (P.aev_len + 3) / 4 * 4;
-    ld_planes = (P.aev_len + 7) / 8 * 8;
+    ld_planes = (P.aev_len + 63) / 64 * 64;   // 128-byte row pitch: every TMA box row starts on a cache-line boundary
     // ---- upload weights in the arithmetic type
     nets.resize(hm.S);
     for (int s = 0; s < hm.S; s++) {
@@ -855,7 +855,7 @@ static int debug_f16_gemm(int device, int R, int N, int K, const float* A, const
   std::vector<float> av(A, A + (size_t)R * K), bv(B, B + (size_t)N * K);
   HalfPlanes a, b;
   const float sa = pick_scale(av) / 64.f, sb = pick_scale(bv);
-  if (upload_half_planes(av, sa, a) || upload_half_planes(bv, sb, b)) return 1;
+  if (upload_half_planes(av, (size_t)K, sa, a) || upload_half_planes(bv, (size_t)K, sb, b)) return 1;
   anib::DevBufTc c_d;
   if (!c_d.reserve((size_t)R * N * 4)) { set_error("out of memory"); return 1; }
   int num_sms = 0, max_smem = 0;
@@ -867,7 +867,7 @@ static int debug_f16_gemm(int device, int R, int N, int K, const float* A, const
   g.R = R; g.N = N; g.num_n_tiles = (N + g.BN - 1) / g.BN; g.num_row_tiles = (R + BM - 1) / BM; g.K = K; g.batch = 1;
   g.acc_scale = 1.0f / (sa * sb);
   const Operand none{nullptr, nullptr, 0, 0, 0};
-  Operand Ao{a.h(), a.l(), (uint64_t)R, (uint64_t)K, (uint64_t)K}, Bo{b.h(), b.l(), (uint64_t)N, (uint64_t)K, (uint64_t)K};
+  Operand Ao{a.h(), a.l(), (uint64_t)R, (uint64_t)K, (uint64_t)pad64(K)}, Bo{b.h(), b.l(), (uint64_t)N, (uint64_t)K, (uint64_t)pad64(K)};
   if (launch_gemm<EPI_D>(L, Ao, Bo, none, c_d.f(), (uint64_t)R, (uint64_t)N, (uint64_t)N, none, g)) return 1;
   ANIB_CUDA_OK(cudaDeviceSynchronize());
   ANIB_CUDA_OK(cudaMemcpy(C, c_d.p, (size_t)R * N * 4, cudaMemcpyDeviceToHost));

@@ -36,12 +36,10 @@ using tc::mbar_arrive; using tc::mbar_expect_tx; using tc::mbar_init; using tc::
 using tc::tc_fence_after; using tc::tc_fence_before; using tc::tma_load_2d; using tc::umma_commit; using tc::umma_desc_sw128;
 
 constexpr int BM = 128;
-constexpr int BKE = 64;                      // halves per k-block = 128 bytes = one swizzle row
-constexpr int kThreads = 256;
-constexpr int kMaxStages = 6;
-constexpr int kAPlaneBytes = BM * 128;       // 16 KB
+constexpr int kMaxThreads = 384;             // 4 control warps + up to 8 epilogue warps
+constexpr int kMaxStages = 8;
 constexpr int kStageBuf = 4096;              // one epilogue staging buffer (32 rows x 128 B, or 2 x 32 rows x 64 B)
-constexpr int kEpiWarps = 4;
+constexpr int kMaxEpiWarps = 8;
 enum { EPI_F = 0, EPI_FO = 1, EPI_B = 2, EPI_D = 3 };
 
 // power-of-two operand scales (see file header)
@@ -51,6 +49,9 @@ struct Args {
   int R, N, BN, num_n_tiles, num_row_tiles, K, batch;
   int a_row0, a_k_off_per_z, b_row_off_per_z;
   int stages, swz;
+  int bk;                // halves per k-block: 64 (128-byte rows, SWIZZLE_128B) or 32 (64-byte rows, SWIZZLE_64B)
+  int epi_warps;         // 4 or 8: with 8, the two warps that own a TMEM lane quadrant take alternate 32-column blocks
+  int out_bufs;          // staging buffers per epilogue warp for the TMA stores (1 or 2)
   int out_col_off_per_z, aux_col_off_per_z;
   float acc_scale;       // accumulator -> true value (x out scale for EPI_B / EPI_D)
   float out_scale;       // EPI_F: scale of the stored H planes; EPI_FO: scale of the stored G planes
@@ -71,6 +72,17 @@ __device__ __forceinline__ void umma_f16(uint32_t tmem_d, uint64_t da, uint64_t 
 // instruction descriptor: D = f32 (1 at bits 4-5), A = B = F16 (0 at bits 7-9, 10-12), both K-major, N>>3 at 17, M>>4 at 24
 __device__ __forceinline__ uint32_t umma_idesc_f16(int M, int N) {
   return (1u << 4) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+// K-major operand tile of 128-byte rows (SWIZZLE_128B, 8-row groups 1024 B apart) or 64-byte rows (SWIZZLE_64B, 512 B apart);
+// descriptor version 1 (sm_100); layout type 2 / 4 (cute/arch/mma_sm100_desc.hpp)
+__device__ __forceinline__ uint64_t umma_desc_k(uint32_t smem_addr, int bk) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr & 0x3FFFF) >> 4);
+  d |= (uint64_t)1 << 16;
+  d |= (uint64_t)((bk == 64 ? 1024 : 512) >> 4) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)(bk == 64 ? 2 : 4) << 61;
+  return d;
 }
 __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
   asm volatile(
@@ -120,7 +132,7 @@ __device__ __forceinline__ uint32_t stage_off(int r, int ch, int row_bytes, int 
 }
 
 template <int EPI>
-__global__ void __launch_bounds__(kThreads, 1)
+__global__ void __launch_bounds__(kMaxThreads, 1)
 f16_gemm_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant__ CUtensorMap tmA_lo,
                 const __grid_constant__ CUtensorMap tmB_hi, const __grid_constant__ CUtensorMap tmB_lo,
                 const __grid_constant__ CUtensorMap tmO_hi, const __grid_constant__ CUtensorMap tmO_lo,
@@ -128,27 +140,29 @@ f16_gemm_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
   extern __shared__ unsigned char smem_raw[];
   const uint32_t raw = smem_u32(smem_raw);
   const uint32_t base = (raw + 1023u) & ~1023u;
-  const uint32_t b_bytes = (uint32_t)g.BN * 128u;
-  const uint32_t stage_bytes = 2u * (kAPlaneBytes + b_bytes);
+  const uint32_t row_bytes = (uint32_t)g.bk * 2u;                 // bytes of one operand row inside a k-block
+  const uint32_t a_bytes = (uint32_t)BM * row_bytes;
+  const uint32_t b_bytes = (uint32_t)g.BN * row_bytes;
+  const uint32_t stage_bytes = 2u * (a_bytes + b_bytes);
   const uint32_t base_out = base + g.stages * stage_bytes;
-  const uint32_t base_aux = base_out + kEpiWarps * 2 * kStageBuf;
-  const uint32_t bar_base = base_aux + (EPI == EPI_B ? kEpiWarps * 2 * kStageBuf : 0);
+  const uint32_t base_aux = base_out + g.epi_warps * g.out_bufs * kStageBuf;
+  const uint32_t bar_base = base_aux + (EPI == EPI_B ? g.epi_warps * 2 * kStageBuf : 0);
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
   auto empty_bar = [&](int s) { return bar_base + 8u * (kMaxStages + s); };
   auto tfull_bar = [&](int s) { return bar_base + 8u * (2 * kMaxStages + s); };
   auto tempty_bar = [&](int s) { return bar_base + 8u * (2 * kMaxStages + 2 + s); };
   auto aux_bar = [&](int w, int b) { return bar_base + 8u * (2 * kMaxStages + 4 + 2 * w + b); };
-  const uint32_t tmem_slot = bar_base + 8u * (2 * kMaxStages + 4 + 2 * kEpiWarps);
+  const uint32_t tmem_slot = bar_base + 8u * (2 * kMaxStages + 4 + 2 * kMaxEpiWarps);
   volatile uint32_t* tmem_slot_ptr = (volatile uint32_t*)(smem_raw + (tmem_slot - raw));
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int num_tiles = g.num_row_tiles * g.num_n_tiles * g.batch;
-  const int KB = (g.K + BKE - 1) / BKE;
+  const int KB = (g.K + g.bk - 1) / g.bk;
 
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < g.stages; s++) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
-    for (int s = 0; s < 2; s++) { mbar_init(tfull_bar(s), 1); mbar_init(tempty_bar(s), kEpiWarps); }
-    for (int w = 0; w < kEpiWarps; w++) { mbar_init(aux_bar(w, 0), 1); mbar_init(aux_bar(w, 1), 1); }
+    for (int s = 0; s < 2; s++) { mbar_init(tfull_bar(s), 1); mbar_init(tempty_bar(s), g.epi_warps); }
+    for (int w = 0; w < g.epi_warps; w++) { mbar_init(aux_bar(w, 0), 1); mbar_init(aux_bar(w, 1), 1); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 2) {
@@ -174,12 +188,12 @@ f16_gemm_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
         for (int kb = 0; kb < KB; kb++) {
           mbar_wait(empty_bar(stage), phase ^ 1u);
           const uint32_t sA = base + stage * stage_bytes;
-          const uint32_t sB = sA + 2 * kAPlaneBytes;
+          const uint32_t sB = sA + 2 * a_bytes;
           mbar_expect_tx(full_bar(stage), stage_bytes);
-          tma_load_2d(&tmA_hi, full_bar(stage), sA, a_col + kb * BKE, a_row);
-          tma_load_2d(&tmB_hi, full_bar(stage), sB, kb * BKE, b_row);
-          tma_load_2d(&tmA_lo, full_bar(stage), sA + kAPlaneBytes, a_col + kb * BKE, a_row);
-          tma_load_2d(&tmB_lo, full_bar(stage), sB + b_bytes, kb * BKE, b_row);
+          tma_load_2d(&tmA_hi, full_bar(stage), sA, a_col + kb * g.bk, a_row);
+          tma_load_2d(&tmB_hi, full_bar(stage), sB, kb * g.bk, b_row);
+          tma_load_2d(&tmA_lo, full_bar(stage), sA + a_bytes, a_col + kb * g.bk, a_row);
+          tma_load_2d(&tmB_lo, full_bar(stage), sB + b_bytes, kb * g.bk, b_row);
           if (++stage == g.stages) { stage = 0; phase ^= 1u; }
         }
       }
@@ -200,10 +214,10 @@ f16_gemm_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
           mbar_wait(full_bar(stage), phase);
           tc_fence_after();
           const uint32_t sA = base + stage * stage_bytes;
-          const uint32_t sB = sA + 2 * kAPlaneBytes;
-          const uint64_t dA_hi = umma_desc_sw128(sA), dB_hi = umma_desc_sw128(sB);
-          const uint64_t dA_lo = umma_desc_sw128(sA + kAPlaneBytes), dB_lo = umma_desc_sw128(sB + b_bytes);
-          const int nks = min(BKE / 16, (g.K - kb * BKE) / 16);   // ragged last k-block: only the valid 16-wide steps
+          const uint32_t sB = sA + 2 * a_bytes;
+          const uint64_t dA_hi = umma_desc_k(sA, g.bk), dB_hi = umma_desc_k(sB, g.bk);
+          const uint64_t dA_lo = umma_desc_k(sA + a_bytes, g.bk), dB_lo = umma_desc_k(sB + b_bytes, g.bk);
+          const int nks = min(g.bk / 16, (g.K - kb * g.bk) / 16);   // ragged last k-block: only the valid 16-wide steps
           for (int k = 0; k < nks; k++) {
             const uint64_t adv = (uint64_t)((k * 32) >> 4);       // 16 halves = 32 bytes along K inside the swizzle row
             umma_f16(tmem_d, dA_hi + adv, dB_hi + adv, idesc, (kb | k) != 0 ? 1u : 0u);
@@ -216,11 +230,12 @@ f16_gemm_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
         umma_commit(tfull_bar(as));           // accumulator complete -> epilogue
       }
     }
-  } else if (warp >= 4) {
+  } else if (warp >= 4 && warp - 4 < g.epi_warps) {
     // ================================================================= epilogue (warp w owns TMEM lanes 32*(w%4)..)
-    const int q = warp & 3;
-    const uint32_t my_out = base_out + (uint32_t)q * 2 * kStageBuf;
-    const uint32_t my_aux = base_aux + (uint32_t)q * 2 * kStageBuf;
+    const int q = warp & 3;                                  // TMEM lane quadrant this warp may read
+    const int ew = warp - 4, half = ew >> 2, nsplit = g.epi_warps >> 2;
+    const uint32_t my_out = base_out + (uint32_t)ew * g.out_bufs * kStageBuf;
+    const uint32_t my_aux = base_aux + (uint32_t)ew * 2 * kStageBuf;
     uint32_t aux_issued = 0, aux_used = 0, store_cnt = 0;
     int it = 0;
     for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, it++) {
@@ -235,22 +250,22 @@ f16_gemm_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
       const int nvalid = min(g.BN / 32, (g.N - nt * g.BN + 31) / 32);
       auto issue_aux = [&](int cb) {
         const uint32_t buf = my_aux + (aux_issued & 1u) * kStageBuf;
-        const uint32_t bar = aux_bar(q, aux_issued & 1u);
+        const uint32_t bar = aux_bar(ew, aux_issued & 1u);
         mbar_expect_tx(bar, kStageBuf);
         tma_load_2d(&tmX_hi, bar, buf, xcol + cb * 32, trow);
         tma_load_2d(&tmX_lo, bar, buf + kStageBuf / 2, xcol + cb * 32, trow);
       };
-      if (EPI == EPI_B) {
-        if (lane == 0) issue_aux(0);
+      if (EPI == EPI_B && half < nvalid) {
+        if (lane == 0) issue_aux(half);
         aux_issued++;
       }
       mbar_wait(tfull_bar(as), aphase);
       tc_fence_after();
       const uint32_t taddr0 = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)as * 256u;
       float e_acc = 0.f;
-      for (int cb = 0; cb < nvalid; cb++) {
-        if (EPI == EPI_B && cb + 1 < nvalid) {
-          if (lane == 0) issue_aux(cb + 1);
+      for (int cb = half; cb < nvalid; cb += nsplit) {
+        if (EPI == EPI_B && cb + nsplit < nvalid) {
+          if (lane == 0) issue_aux(cb + nsplit);
           aux_issued++;
         }
         uint32_t v[32];
@@ -275,7 +290,7 @@ f16_gemm_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
           }
         } else if (EPI == EPI_B) {
           const uint32_t buf = my_aux + (aux_used & 1u) * kStageBuf;
-          mbar_wait(aux_bar(q, aux_used & 1u), (aux_used >> 1) & 1u);
+          mbar_wait(aux_bar(ew, aux_used & 1u), (aux_used >> 1) & 1u);
           aux_used++;
 #pragma unroll
           for (int ch = 0; ch < 4; ch++) {
@@ -295,8 +310,11 @@ f16_gemm_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
           for (int c = 0; c < 32; c++) o[c] = __uint_as_float(v[c]) * g.acc_scale;
         }
         // ---- registers -> swizzled staging -> TMA store
-        const uint32_t sbuf = my_out + (store_cnt & 1u) * kStageBuf;
-        if (store_cnt >= 2 && lane == 0) tma_store_wait_read<1>();
+        const uint32_t sbuf = my_out + (g.out_bufs == 2 ? (store_cnt & 1u) : 0u) * kStageBuf;
+        if (lane == 0) {
+          if (g.out_bufs == 2) { if (store_cnt >= 2) tma_store_wait_read<1>(); }
+          else if (store_cnt >= 1) tma_store_wait_read<0>();
+        }
         __syncwarp();
         if (EPI == EPI_D) {
 #pragma unroll
@@ -330,9 +348,9 @@ f16_gemm_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(tempty_bar(as));
-      if (EPI == EPI_FO) {
+      if (EPI == EPI_FO) {                       // e_out is zeroed before the launch; the warps of a quadrant add their halves
         const int r = trow + lane;
-        if (r < g.R) g.e_out[(size_t)r * g.e_ld + z] = e_acc + __ldg(g.b_out + z);
+        if (r < g.R) atomicAdd(g.e_out + (size_t)r * g.e_ld + z, e_acc + (half == 0 ? __ldg(g.b_out + z) : 0.f));
       }
     }
     if (lane == 0) tma_store_wait_all();
@@ -388,8 +406,13 @@ inline int make_map(CUtensorMap* tm, const void* ptr, CUtensorMapDataType dt, in
   }
   return 0;
 }
-inline int make_operand_map(CUtensorMap* tm, const __half* p, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_rows) {
-  return make_map(tm, p, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, rows, cols, ld, BKE, box_rows, CU_TENSOR_MAP_SWIZZLE_128B);
+inline int make_operand_map(CUtensorMap* tm, const __half* p, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_rows, int bk) {
+  return make_map(tm, p, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, rows, cols, ld, (uint32_t)bk, box_rows,
+                  bk == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B);
+}
+inline int env_int(const char* name, int dflt) {
+  const char* e = getenv(name);
+  return (e && *e) ? atoi(e) : dflt;
 }
 
 inline int epi_swizzle() {
@@ -407,16 +430,21 @@ inline float pick_scale(const std::vector<float>& w) {
   e = std::max(-24, std::min(24, e));
   return std::ldexp(1.f, e);
 }
-inline int upload_half_planes(const std::vector<float>& w, float scale, HalfPlanes& out) {
-  std::vector<__half> h(w.size()), l(w.size());
-  for (size_t i = 0; i < w.size(); i++) {
-    const float x = w[i] * scale;
-    h[i] = __float2half_rn(x);
-    l[i] = __float2half_rn(x - __half2float(h[i]));
-  }
-  if (!out.reserve(std::max<size_t>(w.size(), 8))) { set_error("out of memory for weight planes"); return 1; }
-  ANIB_CUDA_OK(cudaMemcpy(out.hi.p, h.data(), w.size() * 2, cudaMemcpyHostToDevice));
-  ANIB_CUDA_OK(cudaMemcpy(out.lo.p, l.data(), w.size() * 2, cudaMemcpyHostToDevice));
+inline size_t pad64(size_t cols) { return (cols + 63) / 64 * 64; }   // 128-byte row pitch: TMA box rows never straddle a line
+
+// w: [rows][cols] row major -> fp16 hi / lo planes of scale * w with row pitch pad64(cols) (zero padded)
+inline int upload_half_planes(const std::vector<float>& w, size_t cols, float scale, HalfPlanes& out) {
+  const size_t rows = cols ? w.size() / cols : 0, ld = pad64(cols);
+  std::vector<__half> h(rows * ld, __float2half_rn(0.f)), l(rows * ld, __float2half_rn(0.f));
+  for (size_t r = 0; r < rows; r++)
+    for (size_t c = 0; c < cols; c++) {
+      const float x = w[r * cols + c] * scale;
+      h[r * ld + c] = __float2half_rn(x);
+      l[r * ld + c] = __float2half_rn(x - __half2float(h[r * ld + c]));
+    }
+  if (!out.reserve(std::max<size_t>(h.size(), 8))) { set_error("out of memory for weight planes"); return 1; }
+  ANIB_CUDA_OK(cudaMemcpy(out.hi.p, h.data(), h.size() * 2, cudaMemcpyHostToDevice));
+  ANIB_CUDA_OK(cudaMemcpy(out.lo.p, l.data(), l.size() * 2, cudaMemcpyHostToDevice));
   return 0;
 }
 
@@ -443,14 +471,14 @@ inline int prepare_species(const HostModel& hm, int M, int s, SpeciesWeights& w)
       memcpy(b.data() + (size_t)m * no, hm.b[m][s][j].data(), (size_t)no * 4);
     }
     w.sw[j] = pick_scale(f);
-    if (upload_half_planes(f, w.sw[j], w.Wf[j])) return 1;
+    if (upload_half_planes(f, (size_t)ni, w.sw[j], w.Wf[j])) return 1;
     if (tc::upload_f32(b, w.bias[j])) return 1;
     if (j >= 1) {
       std::vector<float> t((size_t)M * ni * no);
       for (int m = 0; m < M; m++)
         for (int o = 0; o < no; o++)
           for (int k = 0; k < ni; k++) t[((size_t)m * ni + k) * no + o] = hm.W[m][s][j][(size_t)o * ni + k];
-      if (upload_half_planes(t, w.sw[j], w.WT[j])) return 1;
+      if (upload_half_planes(t, (size_t)no, w.sw[j], w.WT[j])) return 1;
     }
   }
   {
@@ -459,7 +487,7 @@ inline int prepare_species(const HostModel& hm, int M, int s, SpeciesWeights& w)
     for (int m = 0; m < M; m++)
       for (int k = 0; k < h1; k++)
         for (int q = 0; q < L; q++) cat[(size_t)q * M * h1 + (size_t)m * h1 + k] = hm.W[m][s][0][(size_t)k * L + q];
-    if (upload_half_planes(cat, w.sw[0], w.Wcat)) return 1;
+    if (upload_half_planes(cat, (size_t)M * h1, w.sw[0], w.Wcat)) return 1;
   }
   {
     const int h = dims[nh];
@@ -489,9 +517,12 @@ inline int launch_gemm(const Launcher& L, const Operand& A, const Operand& B, co
                        uint64_t o_cols, uint64_t o_ld, const Operand& X, Args g) {
   CUtensorMap tA_hi, tA_lo, tB_hi, tB_lo, tO_hi, tO_lo, tX_hi, tX_lo;
   g.swz = epi_swizzle();
-  if (make_operand_map(&tA_hi, A.hi, A.rows, A.cols, A.ld, BM) || make_operand_map(&tA_lo, A.lo, A.rows, A.cols, A.ld, BM) ||
-      make_operand_map(&tB_hi, B.hi, B.rows, B.cols, B.ld, (uint32_t)g.BN) ||
-      make_operand_map(&tB_lo, B.lo, B.rows, B.cols, B.ld, (uint32_t)g.BN))
+  static const int cfg_bk = env_int("ANI_B200_BK", 32), cfg_epi = env_int("ANI_B200_EPI_WARPS", 8);
+  g.bk = (cfg_bk == 64) ? 64 : 32;
+  g.epi_warps = (cfg_epi == 4) ? 4 : 8;
+  if (make_operand_map(&tA_hi, A.hi, A.rows, A.cols, A.ld, BM, g.bk) || make_operand_map(&tA_lo, A.lo, A.rows, A.cols, A.ld, BM, g.bk) ||
+      make_operand_map(&tB_hi, B.hi, B.rows, B.cols, B.ld, (uint32_t)g.BN, g.bk) ||
+      make_operand_map(&tB_lo, B.lo, B.rows, B.cols, B.ld, (uint32_t)g.BN, g.bk))
     return 1;
   if (EPI == EPI_D) {
     if (make_map(&tO_hi, out_f32, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, o_rows, o_cols, o_ld, 32, 32,
@@ -512,17 +543,21 @@ inline int launch_gemm(const Launcher& L, const Operand& A, const Operand& B, co
   } else {
     tX_hi = tO_hi; tX_lo = tO_lo;
   }
-  const int stage_bytes = 2 * (kAPlaneBytes + g.BN * 128);
-  const int fixed = 1024 /*alignment*/ + kEpiWarps * 2 * kStageBuf * (EPI == EPI_B ? 2 : 1) + 256 /*barriers*/;
-  int stages = (L.max_smem - fixed) / stage_bytes;
-  stages = std::min(stages, kMaxStages);
+  const int stage_bytes = 2 * (BM + g.BN) * g.bk * 2;
+  const int want = (g.bk == 64) ? 2 : 4;       // k-blocks that should be in flight to cover the L2 -> smem latency
+  int fixed = 0, stages = 0;
+  for (g.out_bufs = 2; g.out_bufs >= 1; g.out_bufs--) {
+    fixed = 1024 /*alignment*/ + g.epi_warps * kStageBuf * (g.out_bufs + (EPI == EPI_B ? 2 : 0)) + 512 /*barriers*/;
+    stages = std::min((L.max_smem - fixed) / stage_bytes, kMaxStages);
+    if (stages >= want || g.out_bufs == 1) break;
+  }
   if (stages < 2) { set_error("not enough shared memory for the f16 tensor-core GEMM pipeline"); return 1; }
   g.stages = stages;
   const int smem = stages * stage_bytes + fixed;
   ANIB_CUDA_OK(cudaFuncSetAttribute(f16_gemm_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
   const int tiles = g.num_row_tiles * g.num_n_tiles * g.batch;
   const int grid = std::max(1, std::min(tiles, L.num_sms));
-  f16_gemm_kernel<EPI><<<grid, kThreads, smem, L.st>>>(tA_hi, tA_lo, tB_hi, tB_lo, tO_hi, tO_lo, tX_hi, tX_lo, g);
+  f16_gemm_kernel<EPI><<<grid, 128 + 32 * g.epi_warps, smem, L.st>>>(tA_hi, tA_lo, tB_hi, tB_lo, tO_hi, tO_lo, tX_hi, tX_lo, g);
   ANIB_CUDA_OK(cudaGetLastError());
   if (L.launches) (*L.launches)++;
   return 0;
@@ -586,7 +621,7 @@ inline int mlp_species(cudaStream_t st, SpeciesWeights& w, Work& work, int M, co
       Operand A = (j == 0) ? Operand{aev_hi, aev_lo, (uint64_t)aev_rows_total, (uint64_t)Lin, (uint64_t)ld_aev}
                            : Operand{work.H[j].h(), work.H[j].l(), (uint64_t)Rc, (uint64_t)M * ni, (uint64_t)M * ni};
       if (j == 0) { g.a_row0 = row0 + r0; g.a_k_off_per_z = 0; } else { g.a_row0 = 0; g.a_k_off_per_z = ni; }
-      Operand B{w.Wf[j].h(), w.Wf[j].l(), (uint64_t)M * no, (uint64_t)ni, (uint64_t)ni};
+      Operand B{w.Wf[j].h(), w.Wf[j].l(), (uint64_t)M * no, (uint64_t)ni, (uint64_t)pad64(ni)};
       int rc;
       if (!last) {
         g.out_scale = kScaleH;
@@ -594,6 +629,7 @@ inline int mlp_species(cudaStream_t st, SpeciesWeights& w, Work& work, int M, co
         rc = launch_gemm<EPI_F>(L, A, B, O, nullptr, 0, 0, 0, none, g);
       } else {
         g.out_scale = kScaleG;
+        ANIB_CUDA_OK(cudaMemsetAsync(work.e.p, 0, (size_t)Rc * M * 4, st));
         g.w_out = w.w_out.f(); g.b_out = w.b_out.f(); g.e_out = work.e.f(); g.e_ld = M;
         Operand O{work.G[nh].h(), work.G[nh].l(), (uint64_t)Rc, (uint64_t)M * no, (uint64_t)M * no};
         rc = launch_gemm<EPI_FO>(L, A, B, O, nullptr, 0, 0, 0, none, g);
@@ -606,15 +642,14 @@ inline int mlp_species(cudaStream_t st, SpeciesWeights& w, Work& work, int M, co
     for (int j = nh - 1; j >= 1; j--) {
       const int ni = dims[j], no = dims[j + 1];   // layer j: ni -> no ; gradient: no -> ni
       Args g{};
-      g.BN = (ni <= 192) ? ni : ni / 2;           // two staging areas (out + aux) leave room for a 192-wide B tile at most
-      if (g.BN % 32 != 0) g.BN = 32;
-      g.R = Rc; g.N = ni; g.num_n_tiles = ni / g.BN; g.num_row_tiles = rtiles; g.K = no; g.batch = M;
+      g.BN = (ni <= 192) ? ni : 128;              // two staging areas (out + aux) leave room for a 192-wide B tile at most
+      g.R = Rc; g.N = ni; g.num_n_tiles = (ni + g.BN - 1) / g.BN; g.num_row_tiles = rtiles; g.K = no; g.batch = M;
       g.a_row0 = 0; g.a_k_off_per_z = no; g.b_row_off_per_z = ni;
       g.acc_scale = 1.0f / w.sw[j];               // (sG * sw) accumulator -> sG-scaled gradient
       g.aux_inv_scale = 1.0f / kScaleH;
       g.out_col_off_per_z = ni; g.aux_col_off_per_z = ni;
       Operand A{work.G[j + 1].h(), work.G[j + 1].l(), (uint64_t)Rc, (uint64_t)M * no, (uint64_t)M * no};
-      Operand B{w.WT[j].h(), w.WT[j].l(), (uint64_t)M * ni, (uint64_t)no, (uint64_t)no};
+      Operand B{w.WT[j].h(), w.WT[j].l(), (uint64_t)M * ni, (uint64_t)no, (uint64_t)pad64(no)};
       Operand O{work.G[j].h(), work.G[j].l(), (uint64_t)Rc, (uint64_t)M * ni, (uint64_t)M * ni};
       Operand X{work.H[j].h(), work.H[j].l(), (uint64_t)Rc, (uint64_t)M * ni, (uint64_t)M * ni};
       if (launch_gemm<EPI_B>(L, A, B, O, nullptr, 0, 0, 0, X, g)) return 1;
@@ -627,7 +662,7 @@ inline int mlp_species(cudaStream_t st, SpeciesWeights& w, Work& work, int M, co
       g.R = Rc; g.N = Lin; g.num_n_tiles = (Lin + g.BN - 1) / g.BN; g.num_row_tiles = rtiles; g.K = M * h1; g.batch = 1;
       g.acc_scale = 1.0f / (kScaleG * w.sw[0] * (float)M);
       Operand A{work.G[1].h(), work.G[1].l(), (uint64_t)Rc, (uint64_t)M * h1, (uint64_t)M * h1};
-      Operand B{w.Wcat.h(), w.Wcat.l(), (uint64_t)Lin, (uint64_t)M * h1, (uint64_t)M * h1};
+      Operand B{w.Wcat.h(), w.Wcat.l(), (uint64_t)Lin, (uint64_t)M * h1, (uint64_t)pad64((size_t)M * h1)};
       if (launch_gemm<EPI_D>(L, A, B, none, daev + (size_t)(row0 + r0) * ld_daev, (uint64_t)Rc, (uint64_t)Lin, (uint64_t)ld_daev, none, g))
         return 1;
     }
