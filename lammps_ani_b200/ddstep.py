@@ -44,7 +44,7 @@ class DomainStep:
         torch.add(self.x.index_select(0, self.send_index), self.send_shift, out=out)
 
     def unpack_add_f(self, buf: torch.Tensor):
-        self.f.index_add_(0, self.send_index, buf)
+        self.f.index_add_(0, self.send_index, buf.clone())   # buf may be a view of f's ghost rows (world == 1)
 
     def forward_halo(self):
         """Ghost positions: x[nlocal:] <- owners' x (+ periodic shift)."""
