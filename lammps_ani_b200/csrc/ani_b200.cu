@@ -18,6 +18,7 @@
 #include "misc.cuh"
 #include "mlp_simt.cuh"
 #include "mlp_f16.cuh"
+#include "mlp_f16_multi.cuh"
 #include "mlp_tc.cuh"
 
 namespace anib {
@@ -132,6 +133,7 @@ struct Engine : EngineBase {
   DevBuf d_H, d_D, d_G;   // MLP intermediates of one chunk
   TcWork tcw;
   f16::Work hwork;
+  std::vector<f16::Work> hring;   // work sets of the chunks in flight in the pipelined MLP
   int64_t ld_planes = 0;   // row pitch of the fp16 AEV planes (multiple of 8 halves = 16 bytes for TMA)
   PinnedBuf h_x, h_f, h_small;
   int64_t ld_aev = 0;
@@ -317,6 +319,7 @@ struct Engine : EngineBase {
 
   int mlp_tc_species(int s, int row0, int R);   // defined for float below
   int mlp_f16_species(int s, int row0, int R);
+  int mlp_f16_all();
   bool aev_in_planes = false;
 
   // ---------------------------------------------------------------------------------------------- one step
@@ -393,6 +396,9 @@ struct Engine : EngineBase {
     }
     if (tm) cudaEventRecord(c->ev[2], st);
     // ---- (2) MLP forward + backward per species bucket
+    if (f16_mode) {
+      if (int rc = mlp_f16_all()) return rc;
+    } else
     for (int s = 0; s < hm.S; s++) {
       const int R = boff[s + 1] - boff[s];
       if (R == 0) continue;
@@ -553,6 +559,74 @@ template <> int Engine<double>::mlp_f16_species(int, int, int) {
 template <> int Engine<float>::mlp_f16_species(int s, int row0, int R) {
   return f16::mlp_species(c->stream, nets[s].hw, hwork, M, nets[s].dims, (const __half*)d_aev_hi.p, (const __half*)d_aev_lo.p,
                           ld_planes, nlocal, row0, R, d_daev.as<float>(), ld_aev, d_eatom.as<double>(), hm.sae[s], &c->launches);
+}
+
+template <> int Engine<double>::mlp_f16_all() {
+  set_error("tensor-core MLP modes are single precision only");
+  return 1;
+}
+
+// All species buckets through the launch-level software pipeline (mlp_f16_multi.cuh); ANI_B200_PIPE=0 or networks of
+// different depth fall back to one bucket after the other.
+template <> int Engine<float>::mlp_f16_all() {
+  static const int pipe = f16::env_int("ANI_B200_PIPE", 0);   // measured slower than bucket-by-bucket (profiles/README.md): off by default
+  int nh = -1;
+  bool same = true;
+  for (int s = 0; s < hm.S; s++) {
+    if (boff[s + 1] == boff[s]) continue;
+    if (!nets[s].hw.ready) { set_error("this network's layer widths are not supported by the f16 tensor-core path (need multiples of 32, <= 256)"); return 1; }
+    if (nh < 0) nh = nets[s].hw.nh; else same = same && (nh == nets[s].hw.nh);
+  }
+  if (nh < 0) return 0;
+  if (!pipe || !same || nh > f16::kMaxProb) {
+    for (int s = 0; s < hm.S; s++) {
+      const int R = boff[s + 1] - boff[s];
+      if (R == 0) continue;
+      if (int rc = mlp_f16_species(s, boff[s], R)) return rc;
+    }
+    return 0;
+  }
+  static const int chunk = (std::max(f16::env_int("ANI_B200_TC_CHUNK", 16384), 128) + 127) / 128 * 128;
+  std::vector<f16::Unit> units;
+  std::vector<int> maxw(nh + 1, 0);
+  int max_rows = 0;
+  for (int s = 0; s < hm.S; s++) {
+    const int R = boff[s + 1] - boff[s];
+    if (R == 0) continue;
+    for (int l = 1; l <= nh; l++) maxw[l] = std::max(maxw[l], nets[s].dims[l]);
+    for (int r0 = 0; r0 < R; r0 += chunk) {
+      units.push_back(f16::Unit{s, boff[s] + r0, std::min(chunk, R - r0)});
+      max_rows = std::max(max_rows, units.back().R);
+    }
+  }
+  const int depth = 2 * nh - 1;
+  const size_t rows = (size_t)(max_rows + 127) / 128 * 128;
+  if ((int)hring.size() < depth) hring.resize(depth);
+  for (int k = 0; k < depth; k++) {
+    f16::Work& wk = hring[k];
+    if ((int)wk.H.size() < nh + 1) { wk.H.resize(nh + 1); wk.G.resize(nh + 1); }
+    for (int l = 1; l <= nh; l++) {
+      const size_t elems = rows * M * maxw[l];
+      if ((l < nh && !wk.H[l].reserve(elems)) || !wk.G[l].reserve(elems)) { set_error("out of memory for MLP work buffers"); return 1; }
+    }
+    if (!wk.e.reserve(rows * M * 4)) { set_error("out of memory for MLP work buffers"); return 1; }
+  }
+  static int num_sms = 0, max_smem = 0;
+  if (!num_sms) {
+    cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, c->device);
+    cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, c->device);
+  }
+  f16::PipeCtx pc{};
+  pc.st = c->stream; pc.M = M;
+  pc.aev_hi = (const __half*)d_aev_hi.p; pc.aev_lo = (const __half*)d_aev_lo.p; pc.ld_aev = ld_planes; pc.aev_rows_total = nlocal;
+  pc.daev = d_daev.as<float>(); pc.ld_daev = ld_aev; pc.eatom = d_eatom.as<double>(); pc.launches = &c->launches;
+  pc.num_sms = num_sms; pc.max_smem = max_smem;
+  pc.bk = f16::env_int("ANI_B200_BK", 32) == 64 ? 64 : 32;
+  pc.swz = f16::epi_swizzle();
+  std::vector<f16::SpeciesWeights*> W(hm.S);
+  std::vector<const std::vector<int>*> dm(hm.S);
+  for (int s = 0; s < hm.S; s++) { W[s] = &nets[s].hw; dm[s] = &nets[s].dims; }
+  return f16::mlp_pipeline(pc, units, W, dm, hm.sae, hring, nh);
 }
 
 template <> int Engine<float>::mlp_tc_species(int s, int row0, int R) {
