@@ -124,7 +124,7 @@ struct Engine : EngineBase {
   int nlocal = 0, ntotal = 0, cap = 32, capA = 64;
   int64_t npairs = 0;
   std::vector<int> boff;   // bucket offsets [S+1] (rows of species s = [boff[s], boff[s+1]))
-  std::vector<int> h_order;
+  std::vector<int> h_order, h_cspecies;
   DevBuf d_species, d_beg, d_cnt, d_jlist, d_order;
   const int* jlist_ptr = nullptr;
   // per-step state
@@ -139,9 +139,23 @@ struct Engine : EngineBase {
   int64_t ld_aev = 0;
   int chunk_rows = 2048;
 
+  // Active-species AEV columns.  An AEV column belongs to one neighbour species (radial) or one unordered pair of
+  // neighbour species (angular); columns of species that occur nowhere in the subdomain (local + ghost) are structurally
+  // zero for every atom, so they -- and the matching columns of every first-layer weight matrix -- are dropped: the AEV
+  // kernels run on the compact species indices cmap[s], rows have Lc = Sp*nR + Sp(Sp+1)/2*nA*nZ columns (water: 128 of
+  // ANI-2x's 1008) and layer 1 / dE/dAEV contract over Lc.  Exact (only zero products are skipped).  The active set only
+  // grows (a superset stays exact); ANI_B200_DENSE_AEV=1 keeps all columns.
+  AevConst<T> Pfull;
+  HostModel hmc;                // hm with the first-layer columns gathered (dims[s][0] = Lc); what the MLP paths upload
+  uint32_t active_mask = 0;
+  std::vector<int> cmap;        // species -> compact index, -1 when absent
+  std::vector<int> col_full;    // compact column -> column of the full AEV
+  bool dense_aev = false;
+
   int aev_gen = 2;   // 2: triple-per-lane kernels (aev2.cuh); 1: the first-generation kernels (aev.cuh), env ANI_B200_AEV=1
   Engine(ani_ctx* ctx, const HostModel& m, int M_) : c(ctx), hm(m), M(M_) {
     if (const char* g = getenv("ANI_B200_AEV")) aev_gen = atoi(g) == 1 ? 1 : 2;
+    if (const char* g = getenv("ANI_B200_DENSE_AEV")) dense_aev = atoi(g) != 0;
     const char* e = getenv("ANI_B200_MLP_CHUNK");
     if (e && atoi(e) > 0) chunk_rows = atoi(e);
   }
@@ -157,24 +171,76 @@ struct Engine : EngineBase {
     P.S = hm.S; P.nR = hm.nR; P.nA = hm.nA; P.nZ = hm.nZ;
     P.rad_len = hm.rad_len(); P.ang_sub = hm.ang_sub(); P.aev_len = hm.aev_len(); P.npairs = hm.S * (hm.S + 1) / 2;
     if (P.ang_sub > 32) { set_error("nShfA*nShfZ > 32 is not supported by the angular kernels"); return 1; }
+    if (hm.S > 31) { set_error("more than 31 species"); return 1; }
     int p = 0;
     for (int s = 0; s < hm.S; s++)
       for (int t = s; t < hm.S; t++) { P.triu[s][t] = p; P.triu[t][s] = p; p++; }
+    Pfull = P;
+    nets.resize(hm.S);
+    ANIB_RESERVE(d_err, sizeof(int));
+    ANIB_CUDA_OK(cudaMemset(d_err.p, 0, sizeof(int)));
+    ANIB_RESERVE(d_scalars, 16 * sizeof(double));
+    ANIB_RESERVE(d_virial, kVirialSlots * 9 * sizeof(double));
+    ANIB_RESERVE(d_partial, 1024 * sizeof(double));
+    return 0;
+  }
+
+  // ---------------------------------------------------------------------------------------------- active species
+  // (Re)build the compact AEV layout for the species in `mask` and upload every network with its first layer gathered.
+  int set_active(uint32_t mask) {
+    active_mask = mask;
+    cmap.assign(hm.S, -1);
+    std::vector<int> act;
+    for (int s = 0; s < hm.S; s++)
+      if (mask >> s & 1u) { cmap[s] = (int)act.size(); act.push_back(s); }
+    const int Sp = (int)act.size();
+    P = Pfull;
+    P.S = Sp; P.rad_len = Sp * P.nR; P.npairs = Sp * (Sp + 1) / 2; P.aev_len = P.rad_len + P.npairs * P.ang_sub;
+    col_full.assign(P.aev_len, 0);
+    for (int a = 0; a < Sp; a++)
+      for (int k = 0; k < P.nR; k++) col_full[a * P.nR + k] = act[a] * Pfull.nR + k;
+    int p = 0;
+    for (int a = 0; a < Sp; a++)
+      for (int b = a; b < Sp; b++) {
+        P.triu[a][b] = p; P.triu[b][a] = p;
+        for (int q = 0; q < P.ang_sub; q++)
+          col_full[P.rad_len + p * P.ang_sub + q] = Pfull.rad_len + Pfull.triu[act[a]][act[b]] * P.ang_sub + q;
+        p++;
+      }
     ld_aev = (P.aev_len + 3) / 4 * 4;
     ld_planes = (P.aev_len + 63) / 64 * 64;   // 128-byte row pitch: every TMA box row starts on a cache-line boundary
-    // ---- upload weights in the arithmetic type
-    nets.resize(hm.S);
+    // gathered copy of the model: only dims / W / b are read from it
+    const int Lc = P.aev_len, Lf = Pfull.aev_len;
+    hmc = hm;
+    for (int s = 0; s < hm.S; s++) {
+      if (hm.dims[s].empty() || hm.dims[s][0] != Lf) { set_error("network input width does not match the AEV length"); return 1; }
+      hmc.dims[s][0] = Lc;
+      const int h1 = hm.dims[s][1];
+      for (size_t m = 0; m < hm.W.size(); m++) {
+        const std::vector<float>& src = hm.W[m][s][0];
+        std::vector<float>& dst = hmc.W[m][s][0];
+        dst.assign((size_t)h1 * Lc, 0.f);
+        for (int k = 0; k < h1; k++)
+          for (int q = 0; q < Lc; q++) dst[(size_t)k * Lc + q] = src[(size_t)k * Lf + col_full[q]];
+      }
+    }
+    return upload_weights(hmc);
+  }
+
+  int upload_tensor_core_planes(const HostModel& src);   // fp32 engine only
+
+  int upload_weights(const HostModel& src) {
     for (int s = 0; s < hm.S; s++) {
       SpeciesNet<T>& n = nets[s];
-      n.dims = hm.dims[s];
+      n.dims = src.dims[s];
       n.nl = (int)n.dims.size() - 1;
       n.W.resize(n.nl); n.b.resize(n.nl); n.WT.resize(n.nl);
       for (int l = 0; l < n.nl; l++) {
         const int ni = n.dims[l], no = n.dims[l + 1];
         std::vector<T> w((size_t)M * no * ni), bb((size_t)M * no);
         for (int m = 0; m < M; m++) {
-          for (size_t q = 0; q < (size_t)no * ni; q++) w[(size_t)m * no * ni + q] = (T)hm.W[m][s][l][q];
-          for (int q = 0; q < no; q++) bb[(size_t)m * no + q] = (T)hm.b[m][s][l][q];
+          for (size_t q = 0; q < (size_t)no * ni; q++) w[(size_t)m * no * ni + q] = (T)src.W[m][s][l][q];
+          for (int q = 0; q < no; q++) bb[(size_t)m * no + q] = (T)src.b[m][s][l][q];
         }
         ANIB_RESERVE(n.W[l], w.size() * sizeof(T));
         ANIB_RESERVE(n.b[l], bb.size() * sizeof(T));
@@ -185,7 +251,7 @@ struct Engine : EngineBase {
           for (int m = 0; m < M; m++)
             for (int o = 0; o < no; o++)
               for (int k = 0; k < ni; k++)
-                wt[((size_t)m * ni + k) * no + o] = (T)hm.W[m][s][l][(size_t)o * ni + k];
+                wt[((size_t)m * ni + k) * no + o] = (T)src.W[m][s][l][(size_t)o * ni + k];
           ANIB_RESERVE(n.WT[l], wt.size() * sizeof(T));
           ANIB_CUDA_OK(cudaMemcpy(n.WT[l].p, wt.data(), wt.size() * sizeof(T), cudaMemcpyHostToDevice));
         }
@@ -195,17 +261,12 @@ struct Engine : EngineBase {
         std::vector<T> cat((size_t)L * M * h1);
         for (int m = 0; m < M; m++)
           for (int k = 0; k < h1; k++)
-            for (int q = 0; q < L; q++) cat[(size_t)q * M * h1 + (size_t)m * h1 + k] = (T)hm.W[m][s][0][(size_t)k * L + q];
+            for (int q = 0; q < L; q++) cat[(size_t)q * M * h1 + (size_t)m * h1 + k] = (T)src.W[m][s][0][(size_t)k * L + q];
         ANIB_RESERVE(n.W1cat, cat.size() * sizeof(T));
         ANIB_CUDA_OK(cudaMemcpy(n.W1cat.p, cat.data(), cat.size() * sizeof(T), cudaMemcpyHostToDevice));
       }
     }
-    ANIB_RESERVE(d_err, sizeof(int));
-    ANIB_CUDA_OK(cudaMemset(d_err.p, 0, sizeof(int)));
-    ANIB_RESERVE(d_scalars, 16 * sizeof(double));
-    ANIB_RESERVE(d_virial, kVirialSlots * 9 * sizeof(double));
-    ANIB_RESERVE(d_partial, 1024 * sizeof(double));
-    return 0;
+    return upload_tensor_core_planes(src);
   }
 
   // ---------------------------------------------------------------------------------------------- rebuild
@@ -223,6 +284,16 @@ struct Engine : EngineBase {
     for (int i = nlocal; i < ntotal; i++)
       if (species_h[i] < 0 || species_h[i] >= hm.S) { set_error("ghost atom has a species index outside the model's species"); return 1; }
     for (int s = 0; s < hm.S; s++) boff[s + 1] += boff[s];
+    {
+      uint32_t present = 0;
+      for (int i = 0; i < ntotal; i++) present |= 1u << species_h[i];
+      if (dense_aev) present = (1u << hm.S) - 1u;
+      if (present == 0) present = 1u;
+      if ((present & ~active_mask) != 0)
+        if (int rc = set_active(active_mask | present)) return rc;
+      h_cspecies.resize(ntotal);
+      for (int i = 0; i < ntotal; i++) h_cspecies[i] = cmap[species_h[i]];
+    }
     h_order.resize(nlocal);
     {
       std::vector<int> cur(boff.begin(), boff.end() - 1);
@@ -237,7 +308,7 @@ struct Engine : EngineBase {
     ANIB_RESERVE(d_cnt, (size_t)std::max(nlocal, 1) * sizeof(int));
     ANIB_RESERVE(d_order, (size_t)std::max(nlocal, 1) * sizeof(int));
     ANIB_RESERVE(d_jlist, (size_t)std::max<int64_t>(npairs, 1) * sizeof(int));
-    ANIB_CUDA_OK(cudaMemcpyAsync(d_species.p, species_h, (size_t)ntotal * sizeof(int), cudaMemcpyHostToDevice, st));
+    ANIB_CUDA_OK(cudaMemcpyAsync(d_species.p, h_cspecies.data(), (size_t)ntotal * sizeof(int), cudaMemcpyHostToDevice, st));   // compact indices
     ANIB_CUDA_OK(cudaMemcpyAsync(d_beg.p, beg_h, (size_t)nlocal * sizeof(int64_t), cudaMemcpyHostToDevice, st));
     ANIB_CUDA_OK(cudaMemcpyAsync(d_cnt.p, cnt_h, (size_t)nlocal * sizeof(int), cudaMemcpyHostToDevice, st));
     ANIB_CUDA_OK(cudaMemcpyAsync(d_order.p, h_order.data(), (size_t)nlocal * sizeof(int), cudaMemcpyHostToDevice, st));
@@ -518,12 +589,15 @@ struct Engine : EngineBase {
   }
   PinnedBuf h_eat;
 
+  // test hook: rows back in atom order and in the FULL AEV layout (dropped columns are zero)
   int get_aev(double* aev, double* daev) override {
     ANIB_CUDA_OK(cudaStreamSynchronize(c->stream));
     std::vector<T> tmp((size_t)nlocal * ld_aev);
+    const int Lf = Pfull.aev_len;
     for (int pass = 0; pass < 2; pass++) {
       double* out = pass == 0 ? aev : daev;
       if (!out) continue;
+      std::fill(out, out + (size_t)nlocal * Lf, 0.0);
       if (pass == 0 && aev_in_planes) {   // f16x3 mode keeps the AEV only as scaled fp16 hi/lo planes
         std::vector<__half> ph((size_t)nlocal * ld_planes), pl((size_t)nlocal * ld_planes);
         ANIB_CUDA_OK(cudaMemcpy(ph.data(), d_aev_hi.p, ph.size() * 2, cudaMemcpyDeviceToHost));
@@ -531,20 +605,28 @@ struct Engine : EngineBase {
         for (int pos = 0; pos < nlocal; pos++) {
           const int i = h_order[pos];
           for (int k = 0; k < P.aev_len; k++)
-            out[(size_t)i * P.aev_len + k] = ((double)__half2float(ph[(size_t)pos * ld_planes + k]) +
-                                              (double)__half2float(pl[(size_t)pos * ld_planes + k])) / (double)f16::kScaleAev;
+            out[(size_t)i * Lf + col_full[k]] = ((double)__half2float(ph[(size_t)pos * ld_planes + k]) +
+                                                 (double)__half2float(pl[(size_t)pos * ld_planes + k])) / (double)f16::kScaleAev;
         }
         continue;
       }
       ANIB_CUDA_OK(cudaMemcpy(tmp.data(), pass == 0 ? d_aev.p : d_daev.p, tmp.size() * sizeof(T), cudaMemcpyDeviceToHost));
       for (int pos = 0; pos < nlocal; pos++) {
         const int i = h_order[pos];
-        for (int k = 0; k < P.aev_len; k++) out[(size_t)i * P.aev_len + k] = (double)tmp[(size_t)pos * ld_aev + k];
+        for (int k = 0; k < P.aev_len; k++) out[(size_t)i * Lf + col_full[k]] = (double)tmp[(size_t)pos * ld_aev + k];
       }
     }
     return 0;
   }
 };
+
+template <> int Engine<double>::upload_tensor_core_planes(const HostModel&) { return 0; }
+template <> int Engine<float>::upload_tensor_core_planes(const HostModel& src) {
+  int rc = 0;
+  for (int s = 0; s < hm.S && !rc; s++) rc = tc_prepare_species(src, M, s, nets[s].tc);
+  for (int s = 0; s < hm.S && !rc; s++) rc = f16::prepare_species(src, M, s, nets[s].hw);
+  return rc;
+}
 
 template <> int Engine<double>::mlp_tc_species(int, int, int) {
   set_error("tensor-core MLP modes are single precision only");
@@ -694,8 +776,6 @@ int ani_ctx_create(const ani_model* model, int device, int use_num_models, int u
     auto* e = new Engine<float>(c.get(), model->hm, M);
     c->eng.reset(e);
     rc = e->init();
-    for (int s = 0; s < model->hm.S && !rc; s++) rc = tc_prepare_species(model->hm, M, s, e->nets[s].tc);
-    for (int s = 0; s < model->hm.S && !rc; s++) rc = f16::prepare_species(model->hm, M, s, e->nets[s].hw);
   } else {
     auto* e = new Engine<double>(c.get(), model->hm, M);
     c->eng.reset(e);

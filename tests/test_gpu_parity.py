@@ -68,16 +68,42 @@ def test_water30_reference_half_list(ANI, water30, ani1xnr_path, single):
     assert np.abs(out[1] - np.array(g["forces"])).max() <= (F_TOL_FP32 if single else 1e-8)
 
 
+def active_columns(species, S, nR, ang_sub):
+    """Columns of the full AEV that belong to species (pairs) present in the system: the library drops the others
+    (structurally zero AEV entries), so its dE/dAEV is defined on these columns only."""
+    act = sorted(set(int(s) for s in species))
+    triu = {}
+    p = 0
+    for a in range(S):
+        for b in range(a, S):
+            triu[(a, b)] = p
+            p += 1
+    cols = [a * nR + k for a in act for k in range(nR)]
+    for i, a in enumerate(act):
+        for b in act[i:]:
+            cols += [S * nR + triu[(a, b)] * ang_sub + q for q in range(ang_sub)]
+    return np.array(sorted(cols))
+
+
+@pytest.mark.parametrize("dense", [False, True])
 @pytest.mark.parametrize("single", [False, True])
 @pytest.mark.parametrize("model", ["ani1xnr", "ani2x_synth"])
-def test_water30_periodic_full_list_with_ghosts(ANI, water30, ani1xnr_path, ani2x_synth_path, single, model):
+def test_water30_periodic_full_list_with_ghosts(ANI, water30, ani1xnr_path, ani2x_synth_path, single, model, dense, monkeypatch):
     path = ani1xnr_path if model == "ani1xnr" else ani2x_synth_path
+    monkeypatch.setenv("ANI_B200_DENSE_AEV", "1" if dense else "0")
     sub, il, nn, jl = periodic_system(water30["x"] + 4.0, water30["species"], [8.0, 8.0, 8.0])
     ref = OracleANI(path).compute_full(sub.species, sub.x, il, nn, jl, sub.nlocal, single_coords=single, want_aev=True,
                                        want_daev=True)
     ani = ANI(path, 0, -1, True, True, single)
     out = ani.compute(sub.species, sub.x, il, jl, nn, nlocal=sub.nlocal, ago=0, atomic=True, vflag=True)
     aev, daev = ani.debug_aev()
+    if not dense:   # dE/dAEV exists only on the columns of the species present (H, O)
+        S, nR = (4, 32) if model == "ani1xnr" else (7, 16)
+        cols = active_columns(sub.species, S, nR, 32)
+        assert len(cols) == 2 * nR + 3 * 32
+        off = np.setdiff1d(np.arange(aev.shape[1]), cols)
+        assert not aev[:, off].any() and not ref["aev"][:, off].any() and not daev[:, off].any()
+        ref["daev"][:, off] = 0.0
     if single:
         assert np.abs(aev - ref["aev"]).max() <= 2e-5 * max(1.0, np.abs(ref["aev"]).max())
         assert np.abs(daev - ref["daev"]).max() <= 2e-5 * max(1.0, np.abs(ref["daev"]).max())
@@ -143,6 +169,34 @@ def test_mixed_species_buckets(ANI, ani2x_synth_path):
         out = ANI(ani2x_synth_path, 0, -1, True, True, single).compute(sub.species, sub.x, il, jl, nn, nlocal=sub.nlocal,
                                                                       atomic=True, vflag=True)
         check(out, ref, single, sub.nlocal)
+
+
+@pytest.mark.parametrize("single", [False, True])
+def test_active_species_subset_and_growth(ANI, ani2x_synth_path, single):
+    """Alanine-dipeptide-like mix (H, C, N, O of ANI-2x's 7 species: 384 of 1008 AEV columns active), then the same context
+    gets a rebuild in which a new species (S) appears: the column layout must grow and stay exact."""
+    rng = np.random.default_rng(17)
+    x, sp, box = domain.make_water_box((5, 5, 4), seed=3)
+    sp = sp.copy()
+    pick = rng.choice(len(sp), size=30, replace=False)
+    sp[pick] = rng.choice([1, 2], size=30)            # C, N among the H (0) / O (3) of the water
+    ani = ANI(ani2x_synth_path, 0, -1, True, True, single)
+    orc = OracleANI(ani2x_synth_path)
+    sub, il, nn, jl = periodic_system(x, sp, box)
+    ref = orc.compute_full(sub.species, sub.x, il, nn, jl, sub.nlocal, single_coords=single)
+    out = ani.compute(sub.species, sub.x, il, jl, nn, nlocal=sub.nlocal, ago=0, atomic=True, vflag=True)
+    check(out, ref, single, sub.nlocal)
+    sp2 = sp.copy()
+    sp2[rng.choice(len(sp), size=5, replace=False)] = 4   # S
+    sub, il, nn, jl = periodic_system(x, sp2, box)
+    ref = orc.compute_full(sub.species, sub.x, il, nn, jl, sub.nlocal, single_coords=single)
+    out = ani.compute(sub.species, sub.x, il, jl, nn, nlocal=sub.nlocal, ago=0, atomic=True, vflag=True)
+    check(out, ref, single, sub.nlocal)
+    # and back to the smaller set: the (now larger) layout stays valid
+    sub, il, nn, jl = periodic_system(x, sp, box)
+    ref = orc.compute_full(sub.species, sub.x, il, nn, jl, sub.nlocal, single_coords=single)
+    out = ani.compute(sub.species, sub.x, il, jl, nn, nlocal=sub.nlocal, ago=0, atomic=True, vflag=True)
+    check(out, ref, single, sub.nlocal)
 
 
 def test_error_paths(ANI, ani1xnr_path, water30):
