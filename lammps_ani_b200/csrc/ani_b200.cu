@@ -19,12 +19,26 @@
 #include "mlp_simt.cuh"
 #include "mlp_f16.cuh"
 #include "mlp_f16_multi.cuh"
+#include "mlp_f16_chain.cuh"
 #include "mlp_tc.cuh"
 
 namespace anib {
 
 static thread_local std::string g_last_error;
-void set_error(const std::string& msg) { g_last_error = msg; }
+static int* (*g_dbg_word_fn)(bool) = nullptr;   // set below: the chained-GEMM wait watchdog's host-mapped word
+void set_error(const std::string& msg) {
+  g_last_error = msg;
+  if (g_dbg_word_fn) {
+    int* w = g_dbg_word_fn(false);
+    for (int i = 0; w && i < 32; i++)
+      if (w[i] != 0) {
+        char buf[96];
+        const unsigned c = (unsigned)w[i];
+        snprintf(buf, sizeof(buf), " [wd warp %u grp %u idx %u line %u]", (c >> 24) & 0x7f, (c >> 20) & 15, (c >> 16) & 15, c & 0xffff);
+        g_last_error += buf;
+      }
+  }
+}
 
 struct DevBuf {
   void* p = nullptr;
@@ -639,6 +653,11 @@ template <> int Engine<double>::mlp_f16_species(int, int, int) {
 }
 
 template <> int Engine<float>::mlp_f16_species(int s, int row0, int R) {
+  g_dbg_word_fn = f16::chain_dbg_word;
+  static const int chain = f16::env_int("ANI_B200_CHAIN", 0);   // 1: chained-layer kernels (mlp_f16_chain.cuh): correct, not yet faster
+  if (chain && f16::chain_supported(nets[s].dims))
+    return f16::mlp_species_chain(c->stream, nets[s].hw, hwork, M, nets[s].dims, (const __half*)d_aev_hi.p, (const __half*)d_aev_lo.p,
+                                  ld_planes, nlocal, row0, R, d_daev.as<float>(), ld_aev, d_eatom.as<double>(), hm.sae[s], &c->launches);
   return f16::mlp_species(c->stream, nets[s].hw, hwork, M, nets[s].dims, (const __half*)d_aev_hi.p, (const __half*)d_aev_lo.p,
                           ld_planes, nlocal, row0, R, d_daev.as<float>(), ld_aev, d_eatom.as<double>(), hm.sae[s], &c->launches);
 }
