@@ -79,6 +79,32 @@ struct PinnedBuf {
     }                                                                                                         \
   } while (0)
 
+// A caller buffer (LAMMPS's x / the pair style's force vector) that was seen at the same address on consecutive calls is
+// page-locked in place (cudaHostRegister) so the H2D / D2H copies go straight from / to it: no staging memcpy, no host
+// conversion loop.  Buffers that move every call keep the pinned-staging path.  ANI_B200_PIN_USER=0 disables.
+struct UserPin {
+  const void* p = nullptr; size_t bytes = 0; bool registered = false; int seen = 0;
+  bool ensure(const void* q, size_t n) {
+    static const bool enabled = !(getenv("ANI_B200_PIN_USER") && atoi(getenv("ANI_B200_PIN_USER")) == 0);
+    if (!enabled || q == nullptr || n == 0) return false;
+    if (q == p && registered && n <= bytes) return true;   // ghost counts shrink and grow between rebuilds
+    if (q == p && n == bytes) {
+      if (++seen < 2) return false;
+      registered = cudaHostRegister((void*)q, n, cudaHostRegisterDefault) == cudaSuccess;
+      if (!registered) { cudaGetLastError(); seen = -1000000; }   // do not retry every step
+      return registered;
+    }
+    release();
+    p = q; bytes = n; seen = 1;
+    return false;
+  }
+  void release() {
+    if (registered) { cudaHostUnregister((void*)p); cudaGetLastError(); }
+    registered = false; p = nullptr; bytes = 0; seen = 0;
+  }
+  ~UserPin() { release(); }
+};
+
 struct EngineBase {
   virtual ~EngineBase() {}
   virtual int set_neighbors(int nlocal, int ntotal, const int* species_h, const int64_t* beg_h, const int* cnt_h,
@@ -150,6 +176,9 @@ struct Engine : EngineBase {
   std::vector<f16::Work> hring;   // work sets of the chunks in flight in the pipelined MLP
   int64_t ld_planes = 0;   // row pitch of the fp16 AEV planes (multiple of 8 halves = 16 bytes for TMA)
   PinnedBuf h_x, h_f, h_small;
+  UserPin pin_x, pin_f;
+  DevBuf d_fout;
+  bool f_direct = false;
   int64_t ld_aev = 0;
   int chunk_rows = 2048;
 
@@ -418,9 +447,13 @@ struct Engine : EngineBase {
     const void* xsrc = x;
     if (!x_on_device) {
       const size_t bytes = (size_t)ntotal * 3 * sizeof(double);
-      ANIB_RESERVE(h_x, bytes);
-      memcpy(h_x.p, x, bytes);   // pageable LAMMPS array -> pinned staging
-      ANIB_CUDA_OK(cudaMemcpyAsync(d_xraw.p, h_x.p, bytes, cudaMemcpyHostToDevice, st));
+      if (pin_x.ensure(x, bytes)) {
+        ANIB_CUDA_OK(cudaMemcpyAsync(d_xraw.p, x, bytes, cudaMemcpyHostToDevice, st));   // DMA straight from the caller's array
+      } else {
+        ANIB_RESERVE(h_x, bytes);
+        memcpy(h_x.p, x, bytes);   // pageable LAMMPS array -> pinned staging
+        ANIB_CUDA_OK(cudaMemcpyAsync(d_xraw.p, h_x.p, bytes, cudaMemcpyHostToDevice, st));
+      }
       xsrc = d_xraw.p;
       x_is_float = false;
     }
@@ -565,7 +598,17 @@ struct Engine : EngineBase {
       need_sync = true;
     }
     ANIB_CUDA_OK(cudaMemcpyAsync(hs + 1, d_err.p, sizeof(int), cudaMemcpyDeviceToHost, st));
-    if (out_force_host != nullptr) {
+    f_direct = false;
+    if (out_force_host != nullptr && ntotal > 0 && pin_f.ensure(out_force_host, (size_t)ntotal * 3 * sizeof(double))) {
+      // widen on the device, DMA straight into the caller's array
+      const int64_t n3 = (int64_t)ntotal * 3;
+      ANIB_RESERVE(d_fout, (size_t)n3 * sizeof(double));
+      convert_kernel<T, double><<<(unsigned)((n3 + 255) / 256), 256, 0, st>>>(d_force.as<T>(), d_fout.as<double>(), n3);
+      c->launches++;
+      ANIB_CUDA_OK(cudaMemcpyAsync(out_force_host, d_fout.p, (size_t)n3 * sizeof(double), cudaMemcpyDeviceToHost, st));
+      f_direct = true;
+      need_sync = true;
+    } else if (out_force_host != nullptr) {
       ANIB_RESERVE(h_f, (size_t)ntotal * 3 * sizeof(T));
       ANIB_CUDA_OK(cudaMemcpyAsync(h_f.p, d_force.p, (size_t)ntotal * 3 * sizeof(T), cudaMemcpyDeviceToHost, st));
       need_sync = true;
@@ -592,7 +635,7 @@ struct Engine : EngineBase {
       for (int a = 0; a < 3; a++)
         for (int b = 0; b < 3; b++) out_virial9[3 * a + b] = 0.5 * (w[3 * a + b] + w[3 * b + a]);
     }
-    if (out_force_host != nullptr) {
+    if (out_force_host != nullptr && !f_direct) {
       const T* src = h_f.as<T>();
       for (size_t k = 0; k < (size_t)ntotal * 3; k++) out_force_host[k] = (double)src[k];
     }

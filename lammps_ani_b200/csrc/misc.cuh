@@ -21,6 +21,13 @@ __global__ void axpy_kernel(const T* __restrict__ src, U* __restrict__ dst, int6
   if (k < n) dst[k] += (U)src[k];
 }
 
+// dst = (U)src   (device-side widening of the force array before a direct D2H into the caller's buffer)
+template <typename T, typename U>
+__global__ void convert_kernel(const T* __restrict__ src, U* __restrict__ dst, int64_t n) {
+  int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (k < n) dst[k] = (U)src[k];
+}
+
 // forward halo: out[k] = x[send_index[k]] + shift[k]   (CommBrick::forward_comm pack with PBC shift, comm_brick.cpp:549-593)
 template <typename T>
 __global__ void halo_pack_kernel(const T* __restrict__ x, const int64_t* __restrict__ idx, const T* __restrict__ shift, int64_t n,

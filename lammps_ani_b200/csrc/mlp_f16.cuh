@@ -592,7 +592,7 @@ inline int mlp_species(cudaStream_t st, SpeciesWeights& w, Work& work, int M, co
   int chunk = work.chunk_rows;
   if (chunk == 0) {
     const char* e = getenv("ANI_B200_TC_CHUNK");
-    chunk = (e && atoi(e) > 0) ? (atoi(e) + BM - 1) / BM * BM : 32768;
+    chunk = (e && atoi(e) > 0) ? (atoi(e) + BM - 1) / BM * BM : 262144;   // measured: fewer, larger launches win (profiles/README.md)
     work.chunk_rows = chunk;
   }
   const int alloc_rows = std::min(chunk, (R + BM - 1) / BM * BM);

@@ -190,7 +190,11 @@ class ANI:
                                                _ptr(ilist), _ptr(numneigh), _ptr(mem), rs, cs, neighmask, 0))
 
     # ---- one step, host arrays (ani.cpp:100-265)
-    def compute(self, species, coordinates, *nbr, nlocal: int, ago: int = 0, atomic: bool = False, vflag: bool = False):
+    def compute(self, species, coordinates, *nbr, nlocal: int, ago: int = 0, atomic: bool = False, vflag: bool = False,
+                out_force=None):
+        """out_force: optional caller-owned float64 [ntotal, 3] array that receives the forces (the reference's
+        `std::vector<double>& out_force`, ani.h); a buffer that stays at the same address from step to step is page-locked by
+        the library and written by DMA."""
         if ago == 0:
             if self.use_fullnbr:
                 ilist, jlist, numneigh = nbr      # argument order of the reference's full overload
@@ -202,7 +206,12 @@ class ANI:
         if x.shape[0] != self.ntotal:
             raise ValueError("coordinates do not match the cached neighbour data (ago != 0 with a different system)")
         energy = C.c_double()
-        force = np.empty((self.ntotal, 3), dtype=np.float64)
+        if out_force is not None:
+            if out_force.dtype != np.float64 or out_force.shape != (self.ntotal, 3) or not out_force.flags.c_contiguous:
+                raise ValueError("out_force must be a C-contiguous float64 array of shape (ntotal, 3)")
+            force = out_force
+        else:
+            force = np.empty((self.ntotal, 3), dtype=np.float64)
         eatom = np.empty(self.nlocal, dtype=np.float64) if atomic else None
         virial = np.empty(9, dtype=np.float64) if vflag else None
         _check(self._L.ani_compute(self._ctx, _ptr(x), C.addressof(energy), _ptr(force), _ptr(eatom), _ptr(virial)))

@@ -199,6 +199,28 @@ def test_active_species_subset_and_growth(ANI, ani2x_synth_path, single):
     check(out, ref, single, sub.nlocal)
 
 
+def test_stable_caller_buffers_are_pinned_in_place(ANI, ani2x_synth_path):
+    """x and out_force at a stable address (LAMMPS's atom->x and the pair style's out_force vector) are page-locked in place
+    from the third call on and moved by DMA: results must be bit-identical to the staged path."""
+    x, sp, box = domain.make_water_box((6, 6, 5), seed=9)
+    sub, il, nn, jl = periodic_system(x, sp, box)
+    ani = ANI(ani2x_synth_path, 0, -1, True, True, True)
+    e0, f0, _, _ = ani.compute(sub.species, sub.x.copy(), il, jl, nn, nlocal=sub.nlocal, ago=0)
+    xs = np.ascontiguousarray(sub.x, dtype=np.float64)
+    fs = np.full((sub.x.shape[0], 3), np.nan)
+    for k in range(5):
+        e, f, _, _ = ani.compute(None, xs, nlocal=sub.nlocal, ago=1, out_force=fs)
+        assert f is fs
+        # forces leave the scatter kernel through fp32 atomics: equal up to summation order
+        assert abs(e - e0) <= 1e-9 * abs(e0) and np.abs(fs - f0).max() <= 1e-4, f"call {k}"
+        fs[:] = np.nan
+    xs[:sub.nlocal] += 1e-3                       # in-place update of the caller's array must be picked up
+    xs[sub.nlocal:] += 1e-3
+    e1, _, _, _ = ani.compute(None, xs, nlocal=sub.nlocal, ago=1, out_force=fs)
+    e2, f2, _, _ = ani.compute(None, xs.copy(), nlocal=sub.nlocal, ago=1)
+    assert abs(e1 - e2) <= 1e-9 * abs(e2) and np.abs(fs - f2).max() <= 1e-4 and abs(e1 - e0) > 1e-6
+
+
 def test_error_paths(ANI, ani1xnr_path, water30):
     ani = ANI(ani1xnr_path, 0)
     sp = water30["species"].copy()
