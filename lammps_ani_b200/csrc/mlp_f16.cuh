@@ -112,11 +112,14 @@ __device__ __forceinline__ void lds128(uint32_t addr, uint32_t& a, uint32_t& b, 
   asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(a), "=r"(b), "=r"(c), "=r"(d) : "r"(addr) : "memory");
 }
 // split x into fp16 hi + lo and pack two neighbouring columns per 32-bit word
+// (packed conversions: F2FP.F16.F32.PACK_AB runs on the ALU, the scalar F2F.F16.F32 on the XU pipe, which the forward
+//  epilogues saturated -- profiles/README.md; results are bit-identical)
 __device__ __forceinline__ void split2(float x0, float x1, uint32_t& hi, uint32_t& lo) {
-  const __half h0 = __float2half_rn(x0), h1 = __float2half_rn(x1);
-  const __half l0 = __float2half_rn(x0 - __half2float(h0)), l1 = __float2half_rn(x1 - __half2float(h1));
-  hi = (uint32_t)__half_as_ushort(h0) | ((uint32_t)__half_as_ushort(h1) << 16);
-  lo = (uint32_t)__half_as_ushort(l0) | ((uint32_t)__half_as_ushort(l1) << 16);
+  const __half2 h = __floats2half2_rn(x0, x1);
+  const float2 hf = __half22float2(h);
+  const __half2 l = __floats2half2_rn(x0 - hf.x, x1 - hf.y);
+  hi = *reinterpret_cast<const uint32_t*>(&h);
+  lo = *reinterpret_cast<const uint32_t*>(&l);
 }
 __device__ __forceinline__ float unpack_sum(uint32_t hi, uint32_t lo, int which) {
   const unsigned short h = which ? (unsigned short)(hi >> 16) : (unsigned short)(hi & 0xFFFFu);
@@ -273,19 +276,27 @@ f16_gemm_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
         const int n0 = nt * g.BN + cb * 32;                    // column inside this member's output
         float o[32];
         if (EPI == EPI_F || EPI == EPI_FO) {
-          const float* bias = g.bias + (size_t)z * g.bias_stride_z + n0;
-          const float* wo = (EPI == EPI_FO) ? g.w_out + (size_t)z * g.N + n0 : nullptr;
+          const float4* bias4 = (const float4*)(g.bias + (size_t)z * g.bias_stride_z + n0);   // 128-byte aligned: widths are multiples of 32
+          const float4* wo4 = (EPI == EPI_FO) ? (const float4*)(g.w_out + (size_t)z * g.N + n0) : nullptr;
+          const float neg_a = 0.1f * g.out_scale;
 #pragma unroll
-          for (int c = 0; c < 32; c++) {
-            const float zz = fmaf(__uint_as_float(v[c]), g.acc_scale, __ldg(bias + c));
-            const float ex = exp2f(zz * 14.426950408889634f);  // e^(z/alpha), alpha = 0.1
-            const float h = zz > 0.f ? zz : 0.1f * (ex - 1.f);
-            if (EPI == EPI_F) {
-              o[c] = h * g.out_scale;
-            } else {
-              const float w = __ldg(wo + c);
-              e_acc = fmaf(h, w, e_acc);
-              o[c] = w * (zz > 0.f ? 1.f : ex) * g.out_scale;
+          for (int c4 = 0; c4 < 8; c4++) {
+            const float4 bq = __ldg(bias4 + c4);
+            const float bb[4] = {bq.x, bq.y, bq.z, bq.w};
+            float ww[4] = {0.f, 0.f, 0.f, 0.f};
+            if (EPI == EPI_FO) { const float4 wq = __ldg(wo4 + c4); ww[0] = wq.x; ww[1] = wq.y; ww[2] = wq.z; ww[3] = wq.w; }
+#pragma unroll
+            for (int k = 0; k < 4; k++) {
+              const int c = 4 * c4 + k;
+              const float zz = fmaf(__uint_as_float(v[c]), g.acc_scale, bb[k]);
+              const float ex = exp2f(zz * 14.426950408889634f);  // e^(z/alpha), alpha = 0.1
+              if (EPI == EPI_F) {
+                o[c] = zz > 0.f ? zz * g.out_scale : fmaf(neg_a, ex, -neg_a);
+              } else {
+                const float h = zz > 0.f ? zz : 0.1f * (ex - 1.f);
+                e_acc = fmaf(h, ww[k], e_acc);
+                o[c] = ww[k] * (zz > 0.f ? 1.f : ex) * g.out_scale;
+              }
             }
           }
         } else if (EPI == EPI_B) {
