@@ -26,7 +26,7 @@ namespace f16 {
 constexpr int kChainMax = 4;
 constexpr int kEpiGroups = 4;                 // epilogue warps per TMEM lane quadrant
 constexpr int kChainThreads = 128 + 128 * kEpiGroups;
-constexpr int kNA = 2;                        // ring depth of the global A operand
+constexpr int kNA = 4;                        // ring depth of the global A operand
 constexpr int kNH = kEpiGroups;               // output-block slots: epilogue group g owns slot g (block cb lives in slot cb % kNH), so
                                               // every waiter of a slot's mbarriers sees each of its phases (no parity aliasing)
 constexpr int kNX = 4;                        // aux loads in flight (they land in the H-ring slot their block will be written to)
@@ -53,6 +53,7 @@ struct ChainArgs {
   int NB;                    // depth of the weight ring (what is left of shared memory)
   int b_slot_bytes;
   int* dbg;                  // host-mapped word for the wait watchdog (may be null)
+  long long* trace;          // optional clock64 stamps of CTA 0's third item (ANI_B200_CHAIN_TRACE=1): [stage][8]
   ChainStage st[kChainMax];
 };
 
@@ -197,6 +198,8 @@ f16_chain_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant__
               mbar_wait_wd(bar(9, S.dep_stage), (occ[S.dep_stage] - 1u) & 1u, g.dbg, WD(9, S.dep_stage));
               tc_fence_after();
             }
+            const bool tr = g.trace != nullptr && blockIdx.x == 0 && it == blockIdx.x + 2 * (int)gridDim.x && zi == 0;
+            if (tr) g.trace[s * 8 + 0] = clock64();                   // stage start (TMEM columns free)
             const uint32_t tmem_d = tmem_base + (uint32_t)S.tmem_col;
             const uint32_t idesc = umma_idesc_f16(BM, S.N);
             const int KB = (S.K + 31) / 32;
@@ -204,6 +207,8 @@ f16_chain_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant__
             for (int kb = 0; kb < KB; kb++) {
               const int sb = (int)(bq % (uint32_t)g.NB);
               mbar_wait_wd(bar(0, sb), (bq / (uint32_t)g.NB) & 1u, g.dbg, WD(0, sb));
+              if (tr && kb == 0) g.trace[s * 8 + 1] = clock64();       // first weight block there
+              if (tr && kb == KB - 1) g.trace[s * 8 + 3] = clock64();  // last weight block there
               uint32_t sA;
               int sa = 0;
               if (S.a_ring) {
@@ -216,6 +221,8 @@ f16_chain_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant__
                 sA = baseA + (uint32_t)sa * kBlkBytes;
               }
               tc_fence_after();
+              if (tr && kb == 0) g.trace[s * 8 + 2] = clock64();       // first A block there
+              if (tr && kb == KB - 1) g.trace[s * 8 + 4] = clock64();  // last A block there (all MMAs issued right after)
               const uint32_t sB = baseB + (uint32_t)sb * g.b_slot_bytes;
               const uint64_t dA_hi = umma_desc_k(sA, 32), dA_lo = umma_desc_k(sA + kBlkBytes / 2, 32);
               const uint64_t dB_hi = umma_desc_k(sB, 32), dB_lo = umma_desc_k(sB + bplane, 32);
@@ -324,10 +331,23 @@ f16_chain_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant__
           const float neg_a = 0.1f * out_scale;
           const float* bias_z = (epi == EPI_F || epi == EPI_FO) ? S.bias + (size_t)z * S.bias_stride_z : nullptr;
           const float* wo_z = (epi == EPI_FO) ? S.w_out + (size_t)z * S.N : nullptr;
-          mbar_wait_wd(bar(8, s), eocc[s] & 1u, g.dbg, WD(8, s));
           if (S.aux_wait_pub) mbar_wait_wd(bar(8, kChainMax), eocc[s] & 1u, g.dbg, WD(8, kChainMax));   // the aux tensor was stored by an earlier stage of this item
+          auto issue_aux = [&](int cb) {
+            // aux block (activations for CELU') straight into the slot this block will be written to: the epilogue works in
+            // place.  Issued by the group itself, in step with its slot's phases (a free-running loader would alias them).
+            mbar_wait_wd(bar(5, grp), (huse & 1u) ^ 1u, g.dbg, WD(5, grp));
+            const uint32_t xbar = bar(6, grp), dst = baseH + (uint32_t)grp * kBlkBytes;
+            mbar_expect_tx(xbar, kBlkBytes);
+            tma_load_2d(&maps.x_hi[s], xbar, dst, z * S.aux_col_off_per_z + cb * 32, rt * BM);
+            tma_load_2d(&maps.x_lo[s], xbar, dst + kBlkBytes / 2, z * S.aux_col_off_per_z + cb * 32, rt * BM);
+          };
+          // the first block's aux load does not need the accumulator: start it while this stage's MMAs are still running
+          if (epi == EPI_B && grp < nbo && q == 0 && lane == 0) issue_aux(grp);
+          mbar_wait_wd(bar(8, s), eocc[s] & 1u, g.dbg, WD(8, s));
           eocc[s]++;
           tc_fence_after();
+          const bool tr = g.trace != nullptr && blockIdx.x == 0 && it == blockIdx.x + 2 * (int)gridDim.x && zi == nz - 1 && warp == 4 && lane == 0;
+          if (tr) g.trace[s * 8 + 5] = clock64();                     // accumulator complete seen by the epilogue
           const uint32_t taddr0 = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)S.tmem_col;
           float e_acc = 0.f;
 #pragma unroll 1
@@ -336,15 +356,7 @@ f16_chain_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant__
             const uint32_t blk = baseH + (uint32_t)slot * kBlkBytes;
             const int xslot = grp;
             const uint32_t xb = blk;             // the aux block was loaded into this very slot
-            if (epi == EPI_B && q == 0 && lane == 0) {
-              // aux block (activations for CELU') straight into the slot this block will be written to: the epilogue works
-              // in place.  Issued here, in step with the ring sequence (a free-running loader would alias mbarrier phases).
-              mbar_wait_wd(bar(5, slot), (huse & 1u) ^ 1u, g.dbg, WD(5, slot));
-              const uint32_t xbar = bar(6, xslot);
-              mbar_expect_tx(xbar, kBlkBytes);
-              tma_load_2d(&maps.x_hi[s], xbar, blk, z * S.aux_col_off_per_z + cb * 32, rt * BM);
-              tma_load_2d(&maps.x_lo[s], xbar, blk + kBlkBytes / 2, z * S.aux_col_off_per_z + cb * 32, rt * BM);
-            }
+            if (epi == EPI_B && cb != grp && q == 0 && lane == 0) issue_aux(cb);
 #pragma unroll 1
             for (int sub = 0; sub < 2; sub++) {
               uint32_t v[16];
@@ -434,6 +446,7 @@ f16_chain_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant__
             if (lane == 0) mbar_arrive(bar(4, slot));
             huse++;
           }
+          if (tr) g.trace[s * 8 + 6] = clock64();                     // this warp's blocks of the stage written
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive(bar(9, s));
@@ -489,6 +502,15 @@ inline int* chain_dbg_word(bool device_ptr) {
 
 inline int launch_chain(const Launcher& L, const ChainMaps& maps, ChainArgs g) {
   g.dbg = chain_dbg_word(true);
+  static const int trace_on = env_int("ANI_B200_CHAIN_TRACE", 0);
+  static long long* trace_dev = nullptr;
+  static int traced = 0;
+  g.trace = nullptr;
+  if (trace_on && traced < 4) {
+    if (!trace_dev) cudaMalloc((void**)&trace_dev, 64 * sizeof(long long));
+    cudaMemsetAsync(trace_dev, 0, 64 * sizeof(long long), L.st);
+    g.trace = trace_dev;
+  }
   int maxN = 0;
   for (int s = 0; s < g.nstages; s++) maxN = std::max(maxN, g.st[s].N);
   g.b_slot_bytes = 2 * maxN * 64;
@@ -502,6 +524,17 @@ inline int launch_chain(const Launcher& L, const ChainMaps& maps, ChainArgs g) {
   const int grid = std::max(1, std::min(items, L.num_sms));
   f16_chain_kernel<<<grid, kChainThreads, smem, L.st>>>(maps, g);
   ANIB_CUDA_OK(cudaGetLastError());
+  if (g.trace) {
+    long long h[64];
+    cudaStreamSynchronize(L.st);
+    cudaMemcpy(h, trace_dev, sizeof(h), cudaMemcpyDeviceToHost);
+    long long t0 = h[0];
+    fprintf(stderr, "[chain trace] launch %d: %d stages, inner_z %d, items %d (cycles relative to stage 0 start of CTA 0's third item)\n", traced, g.nstages, g.inner_z, items);
+    for (int s = 0; s < g.nstages; s++)
+      fprintf(stderr, "  stage %d (K %d N %d): start %lld  B0 %lld  A0 %lld  Blast %lld  Alast %lld | epi: acc seen %lld  done %lld\n", s, g.st[s].K, g.st[s].N,
+              h[s * 8] - t0, h[s * 8 + 1] - t0, h[s * 8 + 2] - t0, h[s * 8 + 3] - t0, h[s * 8 + 4] - t0, h[s * 8 + 5] - t0, h[s * 8 + 6] - t0);
+    traced++;
+  }
   if (L.launches) (*L.launches)++;
   return 0;
 }
