@@ -77,6 +77,11 @@ def active_aev_length(params, species_all):
     return sp * (params.radial_length // params.num_species) + sp * (sp + 1) // 2 * params.angular_sublength
 
 
+def domain_list_cutoff():
+    from lammps_ani_b200 import domain
+    return domain.LIST_CUTOFF
+
+
 def flops_per_step(params, species_local, M, in_len=None):
     """fwd 2*MACs + dE/dAEV backward 2*MACs per member.  in_len: contraction length of the first layer
     (None: the full AEV as the reference executes it; the library contracts over the active columns only)."""
@@ -279,6 +284,20 @@ def main():
         stage += np.array(t)
     stage /= nst
     ani.enable_timing(False)
+    # ---------------- rebuild step (`neighbor->ago == 0`): list built on the device from the device coordinates (row f2)
+    # against installing a host-built list (the reference's path: host flatten + H2D of the list, pair_ani.cpp:107-151)
+    lo_bb, hi_bb = sub.x.min(0) - 1e-6, sub.x.max(0) + 1e-6
+    ani.build_neighbors(sub.species, None, nlocal, domain_list_cutoff(), lo=lo_bb, hi=hi_bb, x_dev_ptr=step.x.data_ptr())   # allocations
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    npairs_dev = ani.build_neighbors(sub.species, None, nlocal, domain_list_cutoff(), lo=lo_bb, hi=hi_bb, x_dev_ptr=step.x.data_ptr())
+    torch.cuda.synchronize()
+    rebuild_dev_ms = (time.perf_counter() - t0) * 1e3
+    t0 = time.perf_counter()
+    ani.set_neighbors_full(sub.species, il, nn, jl, nlocal)
+    torch.cuda.synchronize()
+    rebuild_host_ms = (time.perf_counter() - t0) * 1e3
+    assert npairs_dev == int(jl.size), "device-built list differs from the host list"
     # ---------------- reduce over ranks (max time)
     tm = torch.tensor([ms, ms_e2e], dtype=torch.float64, device=dev)
     cnt = torch.tensor([float(nlocal)], dtype=torch.float64, device=dev)
@@ -329,7 +348,11 @@ def main():
                             "them, see achieved_on_dense_definition"}
         stages = {"pack_ms": stage[0], "aev_fwd_ms": stage[1], "mlp_ms": stage[2], "aev_bwd_ms": stage[3], "reduce_d2h_ms": stage[4],
                   "aev_fwd_GBps": aev_bytes / (max(stage[1], 1e-9) * 1e-3) / 1e9, "aev_bwd_GBps": bwd_bytes / (max(stage[3], 1e-9) * 1e-3) / 1e9,
-                  "hbm_peak_GBps": hbm}
+                  "hbm_peak_GBps": hbm,
+                  "rebuild_device_list_ms": rebuild_dev_ms, "rebuild_host_list_install_ms": rebuild_host_ms,
+                  "rebuild_note": "wall ms of one neigh rebuild: ani_build_neighbors (cell list + search on the device from device "
+                                  "x) vs ani_set_neighbors_full of a ready host list (species bucketing + H2D of the list); the "
+                                  "host-side construction of that list is not included in the second number"}
         line = {
             "metric": "ANI-2x water atom-timesteps/s", "value": value, "unit": "atom-timesteps/s", "n_gpus": world,
             "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True,

@@ -83,6 +83,17 @@ int ani_set_neighbors_table(ani_ctx* ctx, int nlocal, int ntotal, const int* typ
                             const int* ilist, const int* numneigh, const int* table, int64_t row_stride,
                             int64_t col_stride, int neighmask, int on_device);
 
+/* Build the full neighbour list ON THE DEVICE and install it: replaces LAMMPS's `neighbor->build`
+ * (npair_full_bin.cpp) + the host flatten of pair_ani.cpp:107-151 + the H2D copy of the list (ani.cpp:216-218).
+ * x: [ntotal][3] doubles, local atoms first, on the host or (x_on_device != 0) on the device; species: host, [ntotal],
+ * 0-based model species.  Every local atom i gets all j != i (local or ghost) with |x_i - x_j| <= cutoff (fp64).
+ * lo / hi: a box that contains every atom (LAMMPS: sublo - cutghost, subhi + cutghost); atoms outside are clamped into the
+ * border cells, which keeps the result correct and only costs time.  npairs_out (optional): stored pairs. */
+int ani_build_neighbors(ani_ctx* ctx, int nlocal, int ntotal, const int* species, const double* x, int x_on_device,
+                        double cutoff, const double lo[3], const double hi[3], int64_t* npairs_out);
+/* Copy the installed full list to host memory: numneigh [nlocal], jlist [npairs] in atom order (tests). */
+int ani_debug_get_neighbors(ani_ctx* ctx, int* out_numneigh, int* out_jlist);
+
 /* Number of usable CUDA devices (rank -> GPU mapping of the pair style, pair_ani.cpp:255-283). */
 int ani_device_count(int* out);
 

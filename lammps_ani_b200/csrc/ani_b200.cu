@@ -21,6 +21,7 @@
 #include "mlp_f16_multi.cuh"
 #include "mlp_f16_chain.cuh"
 #include "mlp_tc.cuh"
+#include "nbuild.cuh"
 
 namespace anib {
 
@@ -112,6 +113,9 @@ struct EngineBase {
   virtual int compute(const void* x, bool x_on_device, bool x_is_float, double* out_energy, double* out_force_host,
                       void* f_dev, bool f_is_float, double* out_eatom_host, double* eatom_dev, double* out_virial9) = 0;
   virtual int get_aev(double* aev, double* daev) = 0;
+  virtual int build_neighbors(int nlocal, int ntotal, const int* species_h, const double* x, bool x_on_device, double cutoff,
+                              const double* lo, const double* hi, int64_t* npairs_out) = 0;
+  virtual int get_neighbors(int* numneigh, int* jlist) = 0;
 };
 
 template <typename T>
@@ -366,6 +370,72 @@ struct Engine : EngineBase {
     ANIB_RESERVE(d_daev, (size_t)std::max(nlocal, 1) * ld_aev * sizeof(T));
     ANIB_RESERVE(d_eatom, (size_t)std::max(nlocal, 1) * sizeof(double));
     ANIB_RESERVE(d_eatom_atom, (size_t)std::max(nlocal, 1) * sizeof(double));
+    return 0;
+  }
+
+  // ---------------------------------------------------------------------------------------------- device neighbour build
+  DevBuf nb_x, nb_cell, nb_atom, nb_cell_s, nb_atom_s, nb_cbeg, nb_cend, nb_cnt, nb_beg, nb_jlist, nb_tmp;
+  int build_neighbors(int nlocal_, int ntotal_, const int* species_h, const double* x, bool x_on_device, double cutoff,
+                      const double* lo, const double* hi, int64_t* npairs_out) override {
+    cudaStream_t st = c->stream;
+    if (!(cutoff > 0.0)) { set_error("ani_build_neighbors: cutoff must be positive"); return 1; }
+    NbGrid G;
+    G.inv_cell = 1.0 / cutoff;            // cubic cells of exactly one cutoff: 27 cells cover every neighbour; atoms outside
+    for (int d = 0; d < 3; d++) {         // [lo, hi) are clamped into the border cells (a monotone map: |delta cell| <= 1 holds)
+      if (!(hi[d] > lo[d])) { set_error("ani_build_neighbors: empty bounding box"); return 1; }
+      G.lo[d] = lo[d];
+      G.n[d] = std::max(1, (int)std::ceil((hi[d] - lo[d]) * G.inv_cell));
+    }
+    const int64_t ncell = (int64_t)G.n[0] * G.n[1] * G.n[2];
+    if (ncell > (int64_t)1 << 30) { set_error("ani_build_neighbors: too many cells"); return 1; }
+    const int nt = std::max(ntotal_, 1);
+    const double* xd = x;
+    if (!x_on_device) {
+      ANIB_RESERVE(nb_x, (size_t)nt * 3 * sizeof(double));
+      ANIB_CUDA_OK(cudaMemcpyAsync(nb_x.p, x, (size_t)ntotal_ * 3 * sizeof(double), cudaMemcpyHostToDevice, st));
+      xd = nb_x.as<double>();
+    }
+    ANIB_RESERVE(nb_cell, (size_t)nt * 4); ANIB_RESERVE(nb_atom, (size_t)nt * 4);
+    ANIB_RESERVE(nb_cell_s, (size_t)nt * 4); ANIB_RESERVE(nb_atom_s, (size_t)nt * 4);
+    ANIB_RESERVE(nb_cbeg, (size_t)ncell * 4); ANIB_RESERVE(nb_cend, (size_t)ncell * 4);
+    ANIB_RESERVE(nb_cnt, (size_t)std::max(nlocal_, 1) * 4); ANIB_RESERVE(nb_beg, (size_t)std::max(nlocal_, 1) * 8);
+    c->h_cnt.assign(std::max(nlocal_, 1), 0);
+    c->h_beg.assign(std::max(nlocal_, 1), 0);
+    int64_t P = 0;
+    if (ntotal_ > 0 && nlocal_ > 0) {
+      nb_cell_id_kernel<<<(ntotal_ + 255) / 256, 256, 0, st>>>(xd, ntotal_, G, nb_cell.as<int>(), nb_atom.as<int>());
+      size_t tmp_bytes = 0;
+      int bits = 1;
+      while (((int64_t)1 << bits) < ncell) bits++;
+      cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, nb_cell.as<int>(), nb_cell_s.as<int>(), nb_atom.as<int>(), nb_atom_s.as<int>(),
+                                      ntotal_, 0, bits, st);
+      ANIB_RESERVE(nb_tmp, tmp_bytes + 16);
+      ANIB_CUDA_OK(cub::DeviceRadixSort::SortPairs(nb_tmp.p, tmp_bytes, nb_cell.as<int>(), nb_cell_s.as<int>(), nb_atom.as<int>(),
+                                                   nb_atom_s.as<int>(), ntotal_, 0, bits, st));
+      ANIB_CUDA_OK(cudaMemsetAsync(nb_cbeg.p, 0, (size_t)ncell * 4, st));
+      ANIB_CUDA_OK(cudaMemsetAsync(nb_cend.p, 0, (size_t)ncell * 4, st));
+      nb_cell_range_kernel<<<(ntotal_ + 255) / 256, 256, 0, st>>>(nb_cell_s.as<int>(), ntotal_, nb_cbeg.as<int>(), nb_cend.as<int>());
+      nb_search_kernel<false><<<(nlocal_ + 127) / 128, 128, 0, st>>>(xd, nlocal_, G, nb_cbeg.as<int>(), nb_cend.as<int>(),
+                                                                   nb_atom_s.as<int>(), cutoff * cutoff, nb_cnt.as<int>(), nullptr, nullptr);
+      ANIB_CUDA_OK(cudaMemcpyAsync(c->h_cnt.data(), nb_cnt.p, (size_t)nlocal_ * 4, cudaMemcpyDeviceToHost, st));
+      ANIB_CUDA_OK(cudaStreamSynchronize(st));
+      for (int i = 0; i < nlocal_; i++) { c->h_beg[i] = P; P += c->h_cnt[i]; }   // the only host pass: nlocal integers
+      ANIB_RESERVE(nb_jlist, (size_t)std::max<int64_t>(P, 1) * 4);
+      ANIB_CUDA_OK(cudaMemcpyAsync(nb_beg.p, c->h_beg.data(), (size_t)nlocal_ * 8, cudaMemcpyHostToDevice, st));
+      nb_search_kernel<true><<<(nlocal_ + 127) / 128, 128, 0, st>>>(xd, nlocal_, G, nb_cbeg.as<int>(), nb_cend.as<int>(),
+                                                                  nb_atom_s.as<int>(), cutoff * cutoff, nullptr, nb_beg.as<int64_t>(),
+                                                                  nb_jlist.as<int>());
+      ANIB_CUDA_OK(cudaGetLastError());
+      c->launches = 4;
+    }
+    if (npairs_out) *npairs_out = P;
+    return set_neighbors(nlocal_, ntotal_, species_h, c->h_beg.data(), c->h_cnt.data(), nb_jlist.as<int>(), P, true);
+  }
+
+  int get_neighbors(int* numneigh, int* jlist) override {
+    ANIB_CUDA_OK(cudaStreamSynchronize(c->stream));
+    if (numneigh && nlocal > 0) ANIB_CUDA_OK(cudaMemcpy(numneigh, d_cnt.p, (size_t)nlocal * 4, cudaMemcpyDeviceToHost));
+    if (jlist && npairs > 0) ANIB_CUDA_OK(cudaMemcpy(jlist, d_jlist.p, (size_t)npairs * 4, cudaMemcpyDeviceToHost));
     return 0;
   }
 
@@ -921,6 +991,22 @@ static int fetch_ints(std::vector<int>& dst, const int* src, size_t n, int on_de
   if (on_device) ANIB_CUDA_OK(cudaMemcpy(dst.data(), src, n * sizeof(int), cudaMemcpyDeviceToHost));
   else memcpy(dst.data(), src, n * sizeof(int));
   return 0;
+}
+
+int ani_build_neighbors(ani_ctx* c, int nlocal, int ntotal, const int* species, const double* x, int x_on_device, double cutoff,
+                        const double lo[3], const double hi[3], int64_t* npairs_out) {
+  if (!c || !species || !lo || !hi || (ntotal > 0 && !x)) { set_error("ani_build_neighbors: null argument"); return 1; }
+  if (!c->use_fullnbr) { set_error("context was created for a half neighbour list"); return 1; }
+  if (nlocal < 0 || ntotal < nlocal) { set_error("ani_build_neighbors: inconsistent sizes"); return 1; }
+  ANIB_CUDA_OK(cudaSetDevice(c->device));
+  c->h_species.assign(species, species + ntotal);
+  return c->eng->build_neighbors(nlocal, ntotal, c->h_species.data(), x, x_on_device != 0, cutoff, lo, hi, npairs_out);
+}
+
+int ani_debug_get_neighbors(ani_ctx* c, int* numneigh, int* jlist) {
+  if (!c) { set_error("null context"); return 1; }
+  ANIB_CUDA_OK(cudaSetDevice(c->device));
+  return c->eng->get_neighbors(numneigh, jlist);
 }
 
 int ani_set_neighbors_full(ani_ctx* c, int nlocal, int ntotal, const int* species, int inum, const int* ilist,

@@ -19,10 +19,13 @@ MASS = {"H": 1.008, "C": 12.011, "N": 14.007, "O": 15.999, "S": 32.06, "F": 18.9
 
 
 class DeviceNVE:
-    def __init__(self, step, masses: np.ndarray, dt_fs: float, temperature: float = 300.0, seed: int = 12345):
+    def __init__(self, step, masses: np.ndarray, dt_fs: float, temperature: float = 300.0, seed: int = 12345,
+                 rebuild_every: int = 0, list_cutoff: float = 7.1):
         """step: a ddstep.GpuDomainStep (owns x [ntotal,3] f64 and f on the device); masses: [nlocal] g/mol."""
         self.step = step
         self.dt = float(dt_fs)
+        self.rebuild_every, self.list_cutoff = int(rebuild_every), float(list_cutoff)
+        self.rebuilds = 0
         dev = step.x.device
         self.nlocal = step.nlocal
         self.m = torch.tensor(masses, dtype=torch.float64, device=dev).reshape(-1, 1)
@@ -33,6 +36,16 @@ class DeviceNVE:
         self.v = v
         self.dtf_over_m = 0.5 * self.dt * FTM2V / self.m
         self.pe = float(self.step.step_gpu(True))                        # forces at t = 0
+
+    def rebuild(self):
+        """`neigh_modify every N`: refresh the ghosts, then build the full list on the device from the device coordinates
+        (ani_build_neighbors).  Atoms do not migrate between subdomains in these short runs."""
+        s = self.step
+        s.forward_halo()
+        xmin, xmax = s.x.min(0).values.cpu().numpy(), s.x.max(0).values.cpu().numpy()
+        s.ani.build_neighbors(s.sub.species, None, self.nlocal, self.list_cutoff, lo=xmin - 1e-6, hi=xmax + 1e-6,
+                              x_dev_ptr=s.x.data_ptr())
+        self.rebuilds += 1
 
     def kinetic(self) -> float:
         return float(0.5 * MVV2E * (self.m * self.v * self.v).sum())
@@ -45,6 +58,8 @@ class DeviceNVE:
             f = s.f[: self.nlocal]
             self.v.addcmul_(f, self.dtf_over_m)                          # FixNVE::initial_integrate
             s.x[: self.nlocal].add_(self.v, alpha=self.dt)
+            if self.rebuild_every and k % self.rebuild_every == 0:
+                self.rebuild()
             want = (k % energy_every == 0) or k == nsteps
             e = s.step_gpu(want)                                         # ghosts refreshed inside (forward halo)
             self.v.addcmul_(s.f[: self.nlocal], self.dtf_over_m)         # FixNVE::final_integrate

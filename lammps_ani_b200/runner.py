@@ -52,6 +52,8 @@ def load_library():
     L.ani_set_neighbors_half.argtypes = [vp, i32, i32, vp, i64, vp, i32]
     L.ani_set_neighbors_table.argtypes = [vp, i32, i32, vp, i32, i32, vp, vp, vp, i64, i64, i32, i32]
     L.ani_device_count.argtypes = [C.POINTER(i32)]
+    L.ani_build_neighbors.argtypes = [vp, i32, i32, vp, vp, i32, C.c_double, vp, vp, C.POINTER(i64)]
+    L.ani_debug_get_neighbors.argtypes = [vp, vp, vp]
     L.ani_compute.argtypes = [vp, vp, vp, vp, vp, vp]
     L.ani_compute_device.argtypes = [vp, vp, i32, vp, i32, vp, vp, vp]
     L.ani_debug_get_aev.argtypes = [vp, vp, vp]
@@ -62,7 +64,8 @@ def load_library():
     for name in ("ani_model_load", "ani_model_info", "ani_ctx_create", "ani_ctx_set_mlp_mode", "ani_ctx_set_stream",
                  "ani_ctx_reset_stream", "ani_ctx_synchronize", "ani_ctx_enable_timing", "ani_last_timing", "ani_set_neighbors_full",
                  "ani_set_neighbors_half", "ani_set_neighbors_table", "ani_device_count", "ani_compute",
-                 "ani_compute_device", "ani_debug_get_aev", "ani_halo_pack_x", "ani_halo_unpack_add_f"):
+                 "ani_compute_device", "ani_debug_get_aev", "ani_halo_pack_x", "ani_halo_unpack_add_f", "ani_build_neighbors",
+                 "ani_debug_get_neighbors"):
         getattr(L, name).restype = i32
     _lib = L
     return L
@@ -73,7 +76,7 @@ EXPORTED_SYMBOLS = [
     "ani_ctx_set_stream", "ani_ctx_reset_stream", "ani_ctx_synchronize", "ani_set_neighbors_full", "ani_set_neighbors_half", "ani_compute",
     "ani_compute_device", "ani_halo_pack_x", "ani_halo_unpack_add_f", "ani_debug_get_aev", "ani_last_timing",
     "ani_ctx_enable_timing", "ani_last_error", "ani_abi_version", "ani_debug_tc_gemm", "ani_set_neighbors_table",
-    "ani_device_count",
+    "ani_device_count", "ani_build_neighbors", "ani_debug_get_neighbors",
 ]
 
 
@@ -166,6 +169,34 @@ class ANI:
         self.nlocal, self.ntotal = int(nlocal), int(species.shape[0])
         _check(self._L.ani_set_neighbors_full(self._ctx, self.nlocal, self.ntotal, _ptr(species), int(ilist.shape[0]),
                                               _ptr(ilist), _ptr(numneigh), _ptr(jlist), int(jlist.shape[0]), 0))
+
+    def build_neighbors(self, species, x, nlocal: int, cutoff: float = 7.1, lo=None, hi=None, x_dev_ptr: int = 0) -> int:
+        """Full neighbour list built on the device and installed; returns the number of stored pairs.
+        x: host float64 [ntotal, 3] (or pass x_dev_ptr, a device pointer to the same layout, plus lo / hi)."""
+        species = np.ascontiguousarray(species, dtype=np.int32)
+        self.nlocal, self.ntotal = int(nlocal), int(species.shape[0])
+        if x_dev_ptr:
+            xp, on_dev = C.c_void_p(x_dev_ptr), 1
+        else:
+            x = np.ascontiguousarray(x, dtype=np.float64).reshape(-1, 3)
+            if lo is None:
+                lo = x.min(0) - 1e-6
+            if hi is None:
+                hi = x.max(0) + 1e-6
+            xp, on_dev = _ptr(x), 0
+        lo = np.ascontiguousarray(lo, dtype=np.float64)
+        hi = np.ascontiguousarray(hi, dtype=np.float64)
+        n = C.c_int64()
+        _check(self._L.ani_build_neighbors(self._ctx, self.nlocal, self.ntotal, _ptr(species), xp, on_dev, float(cutoff),
+                                           _ptr(lo), _ptr(hi), C.byref(n)))
+        self.npairs = int(n.value)
+        return self.npairs
+
+    def debug_neighbors(self):
+        nn = np.empty(self.nlocal, dtype=np.int32)
+        jl = np.empty(max(self.npairs, 1), dtype=np.int32)
+        _check(self._L.ani_debug_get_neighbors(self._ctx, _ptr(nn), _ptr(jl)))
+        return nn, jl[: self.npairs]
 
     def set_neighbors_half(self, species, atom_index12, nlocal: int):
         species = np.ascontiguousarray(species, dtype=np.int32)

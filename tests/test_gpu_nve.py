@@ -25,7 +25,7 @@ DEV_TOL = {"simt": 0.0, "f16x3": 2e-5, "tf32x3": 2e-5, "tf32": 4e-4}
 _cache = {}
 
 
-def run_mode(path, mode):
+def run_mode(path, mode, rebuild_every=0):
     x, sp, box = domain.make_water_box((6, 6, 6), seed=21, jitter=0.1)
     sub = domain.decompose(x, sp, box, (1, 1, 1))[0]
     halo = domain.replica_halo(sub, box, (1, 1, 1), 0)
@@ -37,7 +37,7 @@ def run_mode(path, mode):
     with torch.cuda.device(dev):
         step = ddstep.GpuDomainStep(ani, sub, halo, dev, il, nn, jl)
         masses = np.where(sub.species[: sub.nlocal] == 0, nve.MASS["H"], nve.MASS["O"])
-        md = nve.DeviceNVE(step, masses, DT, temperature=300.0, seed=7)
+        md = nve.DeviceNVE(step, masses, DT, temperature=300.0, seed=7, rebuild_every=rebuild_every)
         traj = md.run(NSTEPS, energy_every=5)
         torch.cuda.synchronize()
     e = np.array([pe + ke for _, pe, ke in traj])
@@ -60,3 +60,15 @@ def test_nve_energy_drift(ani1xnr_path, mode):
     assert swing > 50 * drift, "the exchange between potential and kinetic energy must dwarf the drift"
     assert drift <= DRIFT_TOL
     assert dev <= DEV_TOL[mode]
+
+
+def test_nve_with_device_neighbor_rebuilds(ani1xnr_path):
+    """Same run with the list rebuilt on the device every 25 steps (rows f2 + f3 together): the conserved quantity must not
+    notice (the list radius exceeds the cutoff by 1.9 A, so the pair SET inside the cutoff is the same either way)."""
+    if "simt" not in _cache:
+        _cache["simt"] = run_mode(ani1xnr_path, "simt")
+    n, e, ke = run_mode(ani1xnr_path, "simt", rebuild_every=25)
+    e_ref = _cache["simt"][1]
+    dev = np.abs((e - e[0]) - (e_ref - e_ref[0])).max() / n
+    print(f"NVE with rebuilds: max |dE-dE_fixed-list| = {dev:.3e} kcal/mol/atom")
+    assert dev <= 5e-6
