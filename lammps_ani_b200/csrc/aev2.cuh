@@ -17,6 +17,10 @@
 
 namespace anib {
 
+// row pitch of the transposed triple-batch buffers f1T[z][triple], f2T[a][triple]: 32 triples + 4 so that the vector reads of
+// the (ShfZ, ShfA) lanes fall into different banks
+constexpr int kAev2TS = 36;
+
 struct Aev2Layout {
   int off_r, off_rfc, off_s, off_a, off_afc, off_as, off_acc, off_f1, off_f2, off_ud, off_us, off_seg;   // forward
   int off_d, off_j, off_adfc, off_ai, off_g;                                                              // backward extras
@@ -34,10 +38,10 @@ __host__ __device__ inline Aev2Layout aev2_layout(int cap, int capA, int acc_ele
   L.off_a = take(capA * 4 * ts, 4 * ts);
   if (backward) L.off_d = take(cap * 4 * ts, 4 * ts);
   else {
-    const int ud = cap * 4 * ts, fb = 32 * (nZ + nA) * ts;
+    const int ud = cap * 4 * ts, fb = kAev2TS * (nZ + nA) * ts;
     L.off_ud = take(ud > fb ? ud : fb, 4 * ts);
     L.off_f1 = L.off_ud;
-    L.off_f2 = L.off_ud + 32 * nZ * ts;
+    L.off_f2 = L.off_ud + kAev2TS * nZ * ts;
   }
   L.off_acc = take(acc_elems * ts, 16);
   L.off_afc = take(capA * ts, 8);
@@ -101,13 +105,13 @@ aev2_forward_kernel(const __grid_constant__ AevConst<T> P, int radial_filter, co
   const unsigned lt = (1u << lane) - 1u;
   int n = 0, na = 0;
   int jn = lane < cnt ? __ldg(jl + lane) : 0;
+  V4 pn = xi;
+  if (lane < cnt) pn = x4[jn];
   for (int b0 = 0; b0 < cnt; b0 += 32) {
     const int e = b0 + lane;
     const bool valid = e < cnt;
-    const int j = jn;
-    if (e + 32 < cnt) jn = __ldg(jl + e + 32);      // next chunk's indices are in flight while this chunk is processed
-    V4 p = xi;
-    if (valid) p = x4[j];
+    const V4 p = pn;
+    if (e + 32 < cnt) { jn = __ldg(jl + e + 32); pn = x4[jn]; }   // next chunk's index and coordinates are in flight meanwhile
     const T dx = p.x - xi.x, dy = p.y - xi.y, dz = p.z - xi.z;
     const T r2 = dx * dx + dy * dy + dz * dz;
     const bool keep = valid && (!radial_filter || r2 <= P.Rcr2) && r2 > T(0);
@@ -205,6 +209,11 @@ aev2_forward_kernel(const __grid_constant__ AevConst<T> P, int radial_filter, co
         int ta = 0, rem = lane;                       // triangular enumeration state (s == t)
         for (int t0 = 0; t0 < ntri; t0 += 32) {
           const int idx = t0 + lane;
+          T f1[NZ], f2[NA];
+#pragma unroll
+          for (int z = 0; z < NZ; z++) f1[z] = T(0);
+#pragma unroll
+          for (int q = 0; q < NA; q++) f2[q] = T(0);
           if (idx < ntri) {
             int a, b;
             if (s == t) {
@@ -219,7 +228,6 @@ aev2_forward_kernel(const __grid_constant__ AevConst<T> P, int radial_filter, co
             const T c = T(0.95) * (A.x * B.x + A.y * B.y + A.z * B.z);
             const T sn = t_sqrt(fmax(T(0), T(1) - c * c));
             const T fcp = T(2) * sh_afc[a] * sh_afc[b];
-            T f1[NZ], f2[NA];
 #pragma unroll
             for (int z = 0; z < NZ; z++) {
               const T u = fmax(T(0), T(0.5) + T(0.5) * (c * P.cosZ[z] + sn * P.sinZ[z]));
@@ -231,23 +239,21 @@ aev2_forward_kernel(const __grid_constant__ AevConst<T> P, int radial_filter, co
               const T dr = ravg - P.ShfA[q];
               f2[q] = t_exp(-P.EtaA * dr * dr);
             }
-            if (NZ % 4 == 0 && NA % 4 == 0) {        // vector stores: no bank conflicts
-#pragma unroll
-              for (int z = 0; z < NZ; z += 4) { V4 v; v.x = f1[z]; v.y = f1[z + 1]; v.z = f1[z + 2]; v.w = f1[z + 3]; *(V4*)(sh_f1 + lane * NZ + z) = v; }
-#pragma unroll
-              for (int q = 0; q < NA; q += 4) { V4 v; v.x = f2[q]; v.y = f2[q + 1]; v.z = f2[q + 2]; v.w = f2[q + 3]; *(V4*)(sh_f2 + lane * NA + q) = v; }
-            } else {
-#pragma unroll
-              for (int z = 0; z < NZ; z++) sh_f1[lane * NZ + z] = f1[z];
-#pragma unroll
-              for (int q = 0; q < NA; q++) sh_f2[lane * NA + q] = f2[q];
-            }
           }
+          // transposed batch buffers (idle lanes write zeros): f1T[z][lane], f2T[a][lane]; consecutive lanes -> consecutive banks
+#pragma unroll
+          for (int z = 0; z < NZ; z++) sh_f1[z * kAev2TS + lane] = f1[z];
+#pragma unroll
+          for (int q = 0; q < NA; q++) sh_f2[q * kAev2TS + lane] = f2[q];
           __syncwarp();
-          const int nb = min(32, ntri - t0);
+          const int nb4 = (min(32, ntri - t0) + 3) >> 2;
           if (lane < NA * NZ) {
-#pragma unroll 4
-            for (int tt = 0; tt < nb; tt++) accr += sh_f1[tt * NZ + iz] * sh_f2[tt * NA + ia];
+            const V4* pa = (const V4*)(sh_f1 + iz * kAev2TS);
+            const V4* pb = (const V4*)(sh_f2 + ia * kAev2TS);
+            for (int tt = 0; tt < nb4; tt++) {       // four triples per pair of vector loads
+              const V4 u = pa[tt], v = pb[tt];
+              accr += u.x * v.x + u.y * v.y + u.z * v.z + u.w * v.w;
+            }
           }
           __syncwarp();
         }
@@ -346,12 +352,15 @@ aev2_backward_kernel(const __grid_constant__ AevConst<T> P, int radial_filter, c
   // ---- gather (as in the forward pass, plus what the gradients need)
   const unsigned lt = (1u << lane) - 1u;
   int n = 0, na = 0;
+  int jn = lane < cnt ? __ldg(jl + lane) : 0;
+  V4 pn = xi;
+  if (lane < cnt) pn = x4[jn];
   for (int b0 = 0; b0 < cnt; b0 += 32) {
     const int e = b0 + lane;
     const bool valid = e < cnt;
-    const int j = valid ? __ldg(jl + e) : 0;
-    V4 p = xi;
-    if (valid) p = x4[j];
+    const int j = jn;
+    const V4 p = pn;
+    if (e + 32 < cnt) { jn = __ldg(jl + e + 32); pn = x4[jn]; }   // next chunk's index and coordinates are in flight meanwhile
     const T dx = p.x - xi.x, dy = p.y - xi.y, dz = p.z - xi.z;
     const T r2 = dx * dx + dy * dy + dz * dz;
     const bool keep = valid && (!radial_filter || r2 <= P.Rcr2) && r2 > T(0);
