@@ -333,8 +333,8 @@ def main():
                     "peak": tf32_peak, "unit": "TFLOP/s", "frac": ach / tf32_peak,
                     # dram__bytes_read + write summed over the stage's 12 GEMM launches of one step, ncu capture of this
                     # workload (profiles/r1_launches_final_300k.csv); null for other sizes / modes
-                    "traffic": 22.93e9 if (args.mlp_mode in ("", "f16x3") and abs(nlocal - 299538) < 10 and M == 8) else None,
-                    "traffic_note": "per step over the stage's launches; 4.9 TB/s = 76 % of the measured HBM peak: the stage is "
+                    "traffic": 23.2e9 if (args.mlp_mode in ("", "f16x3") and abs(nlocal - 299538) < 10 and M == 8) else None,
+                    "traffic_note": "per step over the stage's launches; 5.2 TB/s = 81 % of the measured HBM peak: the stage is "
                                     "bound by its own fp16 hi/lo intermediates (10.2 KB per atom-member), not by the tensor pipe",
                     "peak_source": (f"{which}: bf16_tflops_sustained (fp16 runs at the bf16 rate)" if args.mlp_mode == "f16x3"
                                     else f"{which}: bf16_tflops_sustained/2 taken as the dense TF32 peak"),
