@@ -84,14 +84,16 @@ struct PinnedBuf {
 // page-locked in place (cudaHostRegister) so the H2D / D2H copies go straight from / to it: no staging memcpy, no host
 // conversion loop.  Buffers that move every call keep the pinned-staging path.  ANI_B200_PIN_USER=0 disables.
 struct UserPin {
-  const void* p = nullptr; size_t bytes = 0; bool registered = false; int seen = 0;
+  const void* p = nullptr; size_t bytes = 0; bool registered = false, foreign = false; int seen = 0;
   bool ensure(const void* q, size_t n) {
     static const bool enabled = !(getenv("ANI_B200_PIN_USER") && atoi(getenv("ANI_B200_PIN_USER")) == 0);
     if (!enabled || q == nullptr || n == 0) return false;
-    if (q == p && registered && n <= bytes) return true;   // ghost counts shrink and grow between rebuilds
+    if (q == p && (registered || foreign) && n <= bytes) return true;   // ghost counts shrink and grow between rebuilds
     if (q == p && n == bytes) {
       if (++seen < 2) return false;
-      registered = cudaHostRegister((void*)q, n, cudaHostRegisterDefault) == cudaSuccess;
+      const cudaError_t rc = cudaHostRegister((void*)q, n, cudaHostRegisterDefault);
+      registered = rc == cudaSuccess;
+      if (rc == cudaErrorHostMemoryAlreadyRegistered) { cudaGetLastError(); foreign = true; return true; }   // the caller pinned it: DMA as is
       if (!registered) { cudaGetLastError(); seen = -1000000; }   // do not retry every step
       return registered;
     }
@@ -101,7 +103,7 @@ struct UserPin {
   }
   void release() {
     if (registered) { cudaHostUnregister((void*)p); cudaGetLastError(); }
-    registered = false; p = nullptr; bytes = 0; seen = 0;
+    registered = false; foreign = false; p = nullptr; bytes = 0; seen = 0;
   }
   ~UserPin() { release(); }
 };
