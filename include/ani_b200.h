@@ -91,6 +91,10 @@ int ani_set_neighbors_table(ani_ctx* ctx, int nlocal, int ntotal, const int* typ
  * border cells, which keeps the result correct and only costs time.  npairs_out (optional): stored pairs. */
 int ani_build_neighbors(ani_ctx* ctx, int nlocal, int ntotal, const int* species, const double* x, int x_on_device,
                         double cutoff, const double lo[3], const double hi[3], int64_t* npairs_out);
+/* Drop the page-locks the library took on caller buffers (ani_compute page-locks an x / out_force array it sees at a stable
+ * address).  Call it BEFORE freeing or reallocating such a buffer (the pair style does when atom->nmax or its out_force vector
+ * grows); harmless otherwise. */
+int ani_ctx_release_host_buffers(ani_ctx* ctx);
 /* Copy the installed full list to host memory: numneigh [nlocal], jlist [npairs] in atom order (tests). */
 int ani_debug_get_neighbors(ani_ctx* ctx, int* out_numneigh, int* out_jlist);
 

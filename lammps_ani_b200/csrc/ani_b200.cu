@@ -118,6 +118,7 @@ struct EngineBase {
   virtual int build_neighbors(int nlocal, int ntotal, const int* species_h, const double* x, bool x_on_device, double cutoff,
                               const double* lo, const double* hi, int64_t* npairs_out) = 0;
   virtual int get_neighbors(int* numneigh, int* jlist) = 0;
+  virtual void release_pins() = 0;
 };
 
 template <typename T>
@@ -393,6 +394,8 @@ struct Engine : EngineBase {
     const int nt = std::max(ntotal_, 1);
     const double* xd = x;
     if (!x_on_device) {
+      // a registration of this array left over from a smaller / moved allocation must go before the copy below touches it
+      if (pin_x.p != nullptr && (pin_x.p != (const void*)x || (size_t)ntotal_ * 3 * sizeof(double) > pin_x.bytes)) pin_x.release();
       ANIB_RESERVE(nb_x, (size_t)nt * 3 * sizeof(double));
       ANIB_CUDA_OK(cudaMemcpyAsync(nb_x.p, x, (size_t)ntotal_ * 3 * sizeof(double), cudaMemcpyHostToDevice, st));
       xd = nb_x.as<double>();
@@ -433,6 +436,8 @@ struct Engine : EngineBase {
     if (npairs_out) *npairs_out = P;
     return set_neighbors(nlocal_, ntotal_, species_h, c->h_beg.data(), c->h_cnt.data(), nb_jlist.as<int>(), P, true);
   }
+
+  void release_pins() override { pin_x.release(); pin_f.release(); }
 
   int get_neighbors(int* numneigh, int* jlist) override {
     ANIB_CUDA_OK(cudaStreamSynchronize(c->stream));
@@ -1003,6 +1008,13 @@ int ani_build_neighbors(ani_ctx* c, int nlocal, int ntotal, const int* species, 
   ANIB_CUDA_OK(cudaSetDevice(c->device));
   c->h_species.assign(species, species + ntotal);
   return c->eng->build_neighbors(nlocal, ntotal, c->h_species.data(), x, x_on_device != 0, cutoff, lo, hi, npairs_out);
+}
+
+int ani_ctx_release_host_buffers(ani_ctx* c) {
+  if (!c) { set_error("null context"); return 1; }
+  ANIB_CUDA_OK(cudaSetDevice(c->device));
+  c->eng->release_pins();
+  return 0;
 }
 
 int ani_debug_get_neighbors(ani_ctx* c, int* numneigh, int* jlist) {

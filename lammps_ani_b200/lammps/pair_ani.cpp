@@ -19,6 +19,8 @@
 #include "memory.h"
 #include "neigh_list.h"
 #include "neighbor.h"
+#include "domain.h"
+#include "comm.h"
 #include "update.h"
 
 #ifdef LMP_KOKKOS
@@ -104,9 +106,11 @@ void PairANIB200::settings(int narg, char** arg) {
     else error->all(FLERR, "ani_aev should be cuaev or pyaev");
   }
   if (narg > 5) {
+    device_list = false;
     if (strcmp(arg[5], "full") == 0) use_fullnbr = true;
     else if (strcmp(arg[5], "half") == 0) use_fullnbr = false;
-    else error->all(FLERR, "ani_neighbor should be full or half");
+    else if (strcmp(arg[5], "device") == 0) { use_fullnbr = true; device_list = true; }   // extension: see init_style()
+    else error->all(FLERR, "ani_neighbor should be full, half or device");
   }
   if (narg > 6) {
     if (strcmp(arg[6], "single") == 0) use_single = true;
@@ -143,6 +147,11 @@ void PairANIB200::init_style() {
   if (force->newton_pair == 1)
     error->all(FLERR, use_fullnbr ? "Pair style ANI requires newton pair off when using full neighbor list"
                                   : "Pair style ANI requires newton pair off when using half neighbor list");
+  // `ani_neighbor device` (not in the reference): no list is requested from LAMMPS at all; on rebuild steps the library builds
+  // the same full list (all j within cutoff + skin of a local i, ghosts included) on the GPU from atom->x
+  // (ani_build_neighbors).  LAMMPS still decides WHEN to rebuild (neigh_modify, displacement check) and still sizes the ghost
+  // shell from cutoff + skin; its own CPU binning / list build and the host flatten + H2D of the list disappear.
+  if (device_list) return;
   if (use_fullnbr) neighbor->add_request(this, NeighConst::REQ_FULL);
   else neighbor->add_request(this);
 }
@@ -162,9 +171,28 @@ void PairANIB200::compute(int eflag, int vflag) {
   const int ntotal = nlocal + atom->nghost;
   double** x = atom->x;
   double** f = atom->f;
+  // the library page-locks atom->x and out_force in place once they are stable: let go before either is reallocated
+  if (atom->nmax != last_nmax || (size_t)ntotal * 3 > out_force.size()) {
+    ani_ctx_release_host_buffers(ctx);
+    last_nmax = atom->nmax;
+  }
   if ((size_t)ntotal * 3 > out_force.size()) out_force.resize((size_t)ntotal * 3 + (size_t)ntotal * 3 / 2);
 
-  if (neighbor->ago == 0) {
+  if (neighbor->ago == 0 && device_list) {
+    const int* type = atom->type;
+    if ((size_t)ntotal > species.size()) species.resize((size_t)ntotal + ntotal / 2);
+    for (int i = 0; i < ntotal; i++) species[i] = type[i] - 1;
+    double lo[3], hi[3];
+    for (int d = 0; d < 3; d++) {
+      lo[d] = domain->sublo[d] - comm->cutghost[d];
+      hi[d] = domain->subhi[d] + comm->cutghost[d];
+    }
+    int64_t np = 0;
+    const double* xf = ntotal > 0 ? &x[0][0] : nullptr;
+    if (ani_build_neighbors(ctx, nlocal, ntotal, species.data(), xf, 0, neighbor->cutneighmax, lo, hi, &np))
+      fail("device neighbour build failed");
+    npairs = np;
+  } else if (neighbor->ago == 0) {
     const int* type = atom->type;
     const int inum = list->inum;
     const int* ilist = list->ilist;

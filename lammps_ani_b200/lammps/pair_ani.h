@@ -42,6 +42,8 @@ class PairANIB200 : public Pair {
   std::string model_file, device_str;
   int use_num_models;
   bool use_cuaev, use_fullnbr, use_single;
+  int last_nmax = -1;
+  bool device_list = false;   // `ani_neighbor device`: the library builds the list on the GPU, none is requested from LAMMPS
   ani_model* model;
   ani_ctx* ctx;
   // flattened neighbour data of the last rebuild (grow-only, x1.5 like pair_ani.cpp:120-127)

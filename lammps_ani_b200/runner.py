@@ -54,6 +54,8 @@ def load_library():
     L.ani_device_count.argtypes = [C.POINTER(i32)]
     L.ani_build_neighbors.argtypes = [vp, i32, i32, vp, vp, i32, C.c_double, vp, vp, C.POINTER(i64)]
     L.ani_debug_get_neighbors.argtypes = [vp, vp, vp]
+    L.ani_ctx_release_host_buffers.argtypes = [vp]
+    L.ani_ctx_release_host_buffers.restype = i32
     L.ani_compute.argtypes = [vp, vp, vp, vp, vp, vp]
     L.ani_compute_device.argtypes = [vp, vp, i32, vp, i32, vp, vp, vp]
     L.ani_debug_get_aev.argtypes = [vp, vp, vp]
@@ -76,7 +78,7 @@ EXPORTED_SYMBOLS = [
     "ani_ctx_set_stream", "ani_ctx_reset_stream", "ani_ctx_synchronize", "ani_set_neighbors_full", "ani_set_neighbors_half", "ani_compute",
     "ani_compute_device", "ani_halo_pack_x", "ani_halo_unpack_add_f", "ani_debug_get_aev", "ani_last_timing",
     "ani_ctx_enable_timing", "ani_last_error", "ani_abi_version", "ani_debug_tc_gemm", "ani_set_neighbors_table",
-    "ani_device_count", "ani_build_neighbors", "ani_debug_get_neighbors",
+    "ani_device_count", "ani_build_neighbors", "ani_debug_get_neighbors", "ani_ctx_release_host_buffers",
 ]
 
 

@@ -67,7 +67,8 @@ def _dump_forces(path):
 
 @pytest.mark.gpu
 @needs_lmp
-@pytest.mark.parametrize("nbr,prec", [("full", "single"), ("half", "double"), ("full", "double")])
+@pytest.mark.parametrize("nbr,prec", [("full", "single"), ("half", "double"), ("full", "double"), ("device", "single"),
+                                      ("device", "double")])
 def test_lammps_run_matches_oracle(tmp_path, ani1xnr_path, nbr, prec):
     r = run_lmp(tmp_path, ani1xnr_path, ("ani_neighbor", nbr), ("ani_precision", prec), ("steps", 4))
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
