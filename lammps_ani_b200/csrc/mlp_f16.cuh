@@ -599,7 +599,8 @@ inline int mlp_species(cudaStream_t st, SpeciesWeights& w, Work& work, int M, co
     cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
   }
   static const int smem_cap_kb = env_int("ANI_B200_GEMM_SMEM_KB", 0);   // experiment: leave shared memory for co-resident kernels
-  Launcher L{st, num_sms, launches, smem_cap_kb > 0 ? std::min(max_smem, smem_cap_kb * 1024) : max_smem};
+  static const int cta_cap = env_int("ANI_B200_GEMM_CTAS", 0);          // experiment: leave whole SMs to kernels on another stream
+  Launcher L{st, cta_cap > 0 ? std::min(num_sms, cta_cap) : num_sms, launches, smem_cap_kb > 0 ? std::min(max_smem, smem_cap_kb * 1024) : max_smem};
   const int nh = w.nh;
   int chunk = work.chunk_rows;
   if (chunk == 0) {
