@@ -64,19 +64,29 @@ __host__ __device__ inline Aev2Layout aev2_layout(int cap, int capA, int acc_ele
 
 constexpr int kAev2Warps = 4;
 
+// Row selection of the two-pass scheme.  Pass 1 runs every row with shared-memory buffers sized from the survivor counts seen in
+// recent steps (more resident warps than with list-sized buffers) and appends a row that does not fit to ovf_rows; pass 2 runs
+// just those rows (sel_rows, *sel_cnt) with list-sized buffers, which always hold (n <= list count).  All pointers null = one
+// pass with the buffers given.
+struct Aev2Rows {
+  int* stats = nullptr;           // [2] running max of (radial, angular) survivors (forward pass only)
+  int* ovf_cnt = nullptr;
+  int* ovf_rows = nullptr;
+  const int* sel_cnt = nullptr;
+  const int* sel_rows = nullptr;
+};
+
 // ------------------------------------------------------------------------------------------------ forward
 template <typename T, int NZ, int NA>
-__global__ void __launch_bounds__(kAev2Warps * 32)
-aev2_forward_kernel(const __grid_constant__ AevConst<T> P, int radial_filter, const typename Vec4T<T>::type* __restrict__ x4,
-                    const int64_t* __restrict__ nbr_beg, const int* __restrict__ nbr_cnt, const int* __restrict__ jlist,
-                    const int* __restrict__ order, int nrows, T* __restrict__ aev, int64_t ld, void* __restrict__ aev_hi,
-                    void* __restrict__ aev_lo, int64_t ld_planes, int plane_mode, float plane_scale, int cap, int capA,
-                    int smem_per_warp, int* __restrict__ errflag) {
+__device__ __forceinline__ void
+aev2_forward_row(const AevConst<T>& P, int radial_filter, const typename Vec4T<T>::type* __restrict__ x4,
+                 const int64_t* __restrict__ nbr_beg, const int* __restrict__ nbr_cnt, const int* __restrict__ jlist,
+                 const int* __restrict__ order, int nrows, T* __restrict__ aev, int64_t ld, void* __restrict__ aev_hi,
+                 void* __restrict__ aev_lo, int64_t ld_planes, int plane_mode, float plane_scale, int cap, int capA,
+                 int smem_per_warp, int* __restrict__ errflag, const Aev2Rows& rs, int row) {
   using V4 = typename Vec4T<T>::type;
   extern __shared__ __align__(32) unsigned char smem_raw[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int row = blockIdx.x * kAev2Warps + warp;
-  if (row >= nrows) return;
   const Aev2Layout L = aev2_layout<T>(cap, capA, P.aev_len, NZ, NA, false);
   unsigned char* base = smem_raw + (size_t)warp * smem_per_warp;
   V4* sh_a = (V4*)(base + L.off_a);
@@ -122,8 +132,10 @@ aev2_forward_kernel(const __grid_constant__ AevConst<T> P, int radial_filter, co
       const int pos = n + __popc(m & lt);
       const int s = unpack_species(p.w);
       V4 d; d.x = dx; d.y = dy; d.z = dz; d.w = t_sqrt(r2);
-      sh_ud[pos] = d;
-      sh_us[pos] = s | (keepa ? 256 : 0);
+      if (pos < cap) {
+        sh_ud[pos] = d;
+        sh_us[pos] = s | (keepa ? 256 : 0);
+      }
       const unsigned grp = __match_any_sync(m, s);
       if ((grp & lt) == 0) run_r[s] += __popc(grp);
       if (keepa) {
@@ -135,7 +147,18 @@ aev2_forward_kernel(const __grid_constant__ AevConst<T> P, int radial_filter, co
     n += __popc(m);
     na += __popc(ma);
   }
-  if (na > capA) { if (lane == 0) atomicExch(errflag, 1); }
+  if (rs.stats != nullptr && lane == 0) {   // running maxima of the survivor counts: the host sizes the next steps' buffers from them
+    if (n > rs.stats[0]) atomicMax(rs.stats + 0, n);
+    if (na > rs.stats[1]) atomicMax(rs.stats + 1, na);
+  }
+  if (n > cap || na > capA) {
+    if (rs.ovf_rows != nullptr) {           // buffers sized from recent steps do not hold this atom: defer it to the second pass
+      if (lane == 0) rs.ovf_rows[atomicAdd(rs.ovf_cnt, 1)] = row;
+      return;
+    }
+    if (lane == 0) atomicExch(errflag, 1);
+    if (n > cap) n = cap;                   // unreachable with list-sized buffers (n <= cnt <= cap)
+  }
   // ---- segment offsets (exclusive prefix over species), run counters reset
   if (lane == 0) {
     int o_r = 0, o_a = 0;
@@ -293,20 +316,42 @@ aev2_forward_kernel(const __grid_constant__ AevConst<T> P, int radial_filter, co
   }
 }
 
+// One warp per row; pass 1 covers all rows with one row per warp, pass 2 strides a small grid over the deferred rows.
+template <typename T, int NZ, int NA, bool STRIDED = false>
+__global__ void __launch_bounds__(kAev2Warps * 32, sizeof(T) == 4 ? 9 : 1)   // fp32: 56 registers -> 36 warps per SM
+aev2_forward_kernel(const __grid_constant__ AevConst<T> P, int radial_filter, const typename Vec4T<T>::type* __restrict__ x4,
+                    const int64_t* __restrict__ nbr_beg, const int* __restrict__ nbr_cnt, const int* __restrict__ jlist,
+                    const int* __restrict__ order, int nrows, T* __restrict__ aev, int64_t ld, void* __restrict__ aev_hi,
+                    void* __restrict__ aev_lo, int64_t ld_planes, int plane_mode, float plane_scale, int cap, int capA,
+                    int smem_per_warp, int* __restrict__ errflag, Aev2Rows rs) {
+  if (!STRIDED) {   // pass 1 (or the only pass): one row per warp
+    const int row = blockIdx.x * kAev2Warps + (threadIdx.x >> 5);
+    if (row < nrows)
+      aev2_forward_row<T, NZ, NA>(P, radial_filter, x4, nbr_beg, nbr_cnt, jlist, order, nrows, aev, ld, aev_hi, aev_lo, ld_planes,
+                                  plane_mode, plane_scale, cap, capA, smem_per_warp, errflag, rs, row);
+    return;
+  }
+  const int nsel = min(*rs.sel_cnt, nrows);
+  for (int slot = blockIdx.x * kAev2Warps + (threadIdx.x >> 5); slot < nsel; slot += gridDim.x * kAev2Warps) {
+    aev2_forward_row<T, NZ, NA>(P, radial_filter, x4, nbr_beg, nbr_cnt, jlist, order, nrows, aev, ld, aev_hi, aev_lo, ld_planes,
+                                plane_mode, plane_scale, cap, capA, smem_per_warp, errflag, rs, rs.sel_rows[slot]);
+    __syncwarp();
+  }
+}
+
 // ------------------------------------------------------------------------------------------------ backward
 // daev: dE/dAEV rows in bucket order (Hartree).  force: T[ntotal*3], accumulated with atomics (kcal/mol/A).
 // virial_slots: double[kVirialSlots*9], accumulated (kcal/mol), or nullptr.
 template <typename T, int NZ, int NA>
-__global__ void __launch_bounds__(kAev2Warps * 32)
-aev2_backward_kernel(const __grid_constant__ AevConst<T> P, int radial_filter, const typename Vec4T<T>::type* __restrict__ x4,
-                     const int64_t* __restrict__ nbr_beg, const int* __restrict__ nbr_cnt, const int* __restrict__ jlist,
-                     const int* __restrict__ order, int nrows, const T* __restrict__ daev, int64_t ld, T* __restrict__ force,
-                     double* __restrict__ virial_slots, T out_scale, int cap, int capA, int smem_per_warp) {
+__device__ __forceinline__ void
+aev2_backward_row(const AevConst<T>& P, int radial_filter, const typename Vec4T<T>::type* __restrict__ x4,
+                  const int64_t* __restrict__ nbr_beg, const int* __restrict__ nbr_cnt, const int* __restrict__ jlist,
+                  const int* __restrict__ order, int nrows, const T* __restrict__ daev, int64_t ld, T* __restrict__ force,
+                  double* __restrict__ virial_slots, T out_scale, int cap, int capA, int smem_per_warp, const Aev2Rows& rs,
+                  int row) {
   using V4 = typename Vec4T<T>::type;
   extern __shared__ __align__(32) unsigned char smem_raw[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int row = blockIdx.x * kAev2Warps + warp;
-  if (row >= nrows) return;
   const int rstride = P.nR + 1;            // padded rows: species / species pairs land in different banks
   constexpr int astride = NA * NZ + 1;
   const int acc_elems = P.S * rstride + P.npairs * astride;
@@ -371,10 +416,12 @@ aev2_backward_kernel(const __grid_constant__ AevConst<T> P, int radial_filter, c
       const int pos = n + __popc(m & lt);
       const T r = t_sqrt(r2);
       V4 d; d.x = dx; d.y = dy; d.z = dz; d.w = r;
-      sh_d[pos] = d;
       const int s = unpack_species(p.w);
-      sh_s[pos] = s;
-      sh_j[pos] = j;
+      if (pos < cap) {
+        sh_d[pos] = d;
+        sh_s[pos] = s;
+        sh_j[pos] = j;
+      }
       if (keepa) {
         const int posa = na + __popc(ma & lt);
         if (posa < capA) {
@@ -393,9 +440,16 @@ aev2_backward_kernel(const __grid_constant__ AevConst<T> P, int radial_filter, c
     n += __popc(m);
     na += __popc(ma);
   }
-  if (na > capA) na = capA;   // the forward pass raised the error flag
   asm volatile("cp.async.wait_all;" ::: "memory");
   __syncwarp();
+  if (n > cap || na > capA) {
+    if (rs.ovf_rows != nullptr) {           // deferred to the second pass (list-sized buffers)
+      if (lane == 0) rs.ovf_rows[atomicAdd(rs.ovf_cnt, 1)] = row;
+      return;
+    }
+    if (na > capA) na = capA;               // the forward pass raised the error flag
+    if (n > cap) n = cap;
+  }
 
   // ---- radial: lane = neighbour
   for (int e = lane; e < n; e += 32) {
@@ -504,6 +558,28 @@ aev2_backward_kernel(const __grid_constant__ AevConst<T> P, int radial_filter, c
       for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
       if (lane == 0) atomicAdd(virial_slots + (size_t)(blockIdx.x % kVirialSlots) * 9 + q, v);
     }
+  }
+}
+
+
+template <typename T, int NZ, int NA, bool STRIDED = false>
+__global__ void __launch_bounds__(kAev2Warps * 32, sizeof(T) == 4 ? 8 : 1)   // fp32: 64 registers -> 32 warps per SM
+aev2_backward_kernel(const __grid_constant__ AevConst<T> P, int radial_filter, const typename Vec4T<T>::type* __restrict__ x4,
+                     const int64_t* __restrict__ nbr_beg, const int* __restrict__ nbr_cnt, const int* __restrict__ jlist,
+                     const int* __restrict__ order, int nrows, const T* __restrict__ daev, int64_t ld, T* __restrict__ force,
+                     double* __restrict__ virial_slots, T out_scale, int cap, int capA, int smem_per_warp, Aev2Rows rs) {
+  if (!STRIDED) {
+    const int row = blockIdx.x * kAev2Warps + (threadIdx.x >> 5);
+    if (row < nrows)
+      aev2_backward_row<T, NZ, NA>(P, radial_filter, x4, nbr_beg, nbr_cnt, jlist, order, nrows, daev, ld, force, virial_slots,
+                                   out_scale, cap, capA, smem_per_warp, rs, row);
+    return;
+  }
+  const int nsel = min(*rs.sel_cnt, nrows);
+  for (int slot = blockIdx.x * kAev2Warps + (threadIdx.x >> 5); slot < nsel; slot += gridDim.x * kAev2Warps) {
+    aev2_backward_row<T, NZ, NA>(P, radial_filter, x4, nbr_beg, nbr_cnt, jlist, order, nrows, daev, ld, force, virial_slots,
+                                 out_scale, cap, capA, smem_per_warp, rs, rs.sel_rows[slot]);
+    __syncwarp();
   }
 }
 

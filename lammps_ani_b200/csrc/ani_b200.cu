@@ -169,6 +169,9 @@ struct Engine : EngineBase {
   std::vector<SpeciesNet<T>> nets;
   // per-rebuild state
   int nlocal = 0, ntotal = 0, cap = 32, capA = 64;
+  int cap_fit = 0, capA_fit = 0;      // buffers sized from the survivor counts of recent steps (0 = unknown yet); see Aev2Rows
+  bool stats_pending = false;
+  DevBuf d_ovf, d_ovf_rows;           // [maxn, maxna, deferred rows fwd, deferred rows bwd]; row lists [2][nlocal]
   int64_t npairs = 0;
   std::vector<int> boff;   // bucket offsets [S+1] (rows of species s = [boff[s], boff[s+1]))
   std::vector<int> h_order, h_cspecies;
@@ -543,6 +546,24 @@ struct Engine : EngineBase {
     ANIB_CUDA_OK(cudaMemsetAsync(d_force.p, 0, (size_t)ntotal * 3 * sizeof(T), st));
     const bool want_virial = out_virial9 != nullptr;
     if (want_virial) ANIB_CUDA_OK(cudaMemsetAsync(d_virial.p, 0, kVirialSlots * 9 * sizeof(double), st));
+    // two-pass AEV kernels: first-pass buffers from the survivor counts the previous steps reported (performance only: a row
+    // that does not fit is redone by the second pass with list-sized buffers)
+    const size_t small_bytes = (4 + kVirialSlots * 9) * sizeof(double);
+    ANIB_RESERVE(h_small, small_bytes);
+    double* hs = h_small.as<double>();
+    if (!stats_pending) memset(hs, 0, small_bytes);
+    if (stats_pending) {
+      const int* hst = (const int*)(hs + 2);
+      const int mn = hst[0], mna = hst[1];
+      if (mn > 0) cap_fit = (mn + std::max(4, mn / 8) + 7) / 8 * 8;
+      if (mn > 0) capA_fit = (mna + std::max(4, mna / 8) + 7) / 8 * 8;
+    }
+    static const bool two_pass_on = f16::env_int("ANI_B200_AEV_TWO_PASS", 1) != 0;
+    const int cap1 = std::min(cap, cap_fit), capA1 = std::min(capA, std::max(capA_fit, 8));
+    const bool two_pass = two_pass_on && aev_gen == 2 && cap_fit > 0 && nlocal > 0 && (cap1 + 16 <= cap || capA1 + 16 <= capA);
+    ANIB_RESERVE(d_ovf, 4 * sizeof(int));
+    ANIB_RESERVE(d_ovf_rows, (size_t)std::max(nlocal, 1) * 2 * sizeof(int));
+    ANIB_CUDA_OK(cudaMemsetAsync(d_ovf.p, 0, 4 * sizeof(int), st));
     if (tm) cudaEventRecord(c->ev[1], st);
     // ---- (1) AEV forward
     const bool f16_mode = (sizeof(T) == 4) && c->mlp_mode == ANI_MLP_F16X3;
@@ -568,19 +589,38 @@ struct Engine : EngineBase {
         ANIB_RESERVE(d_aev_lo, (size_t)tc_padded_rows(nlocal, hm.S) * ld_aev * sizeof(float));
         hi = d_aev_hi.p; lo = d_aev_lo.p; plane_mode = 1;
       }
-      auto launch2 = [&](auto kern) -> int {
+      auto launch2 = [&](auto kern, auto kern_strided) -> int {
         const Aev2Layout L2 = aev2_layout<T>(cap, capA, P.aev_len, P.nZ, P.nA, false);
         const int smem2 = L2.bytes * kAev2Warps;
         ANIB_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem2));
-        kern<<<(nlocal + kAev2Warps - 1) / kAev2Warps, kAev2Warps * 32, smem2, st>>>(
-            P, c->use_cuaev ? 1 : 0, d_x4.as<V4>(), d_beg.as<int64_t>(), d_cnt.as<int>(), d_jlist.as<int>(), d_order.as<int>(),
-            nlocal, rows, ld_aev, hi, lo, ldp, plane_mode, f16::kScaleAev, cap, capA, L2.bytes, d_err.as<int>());
+        const int grid = (nlocal + kAev2Warps - 1) / kAev2Warps;
+        Aev2Rows rs;
+        rs.stats = d_ovf.as<int>();
+        if (two_pass) {   // pass 1: buffers that fit recent steps; rows that do not fit are deferred
+          const Aev2Layout L1 = aev2_layout<T>(cap1, capA1, P.aev_len, P.nZ, P.nA, false);
+          rs.ovf_cnt = d_ovf.as<int>() + 2; rs.ovf_rows = d_ovf_rows.as<int>();
+          kern<<<grid, kAev2Warps * 32, L1.bytes * kAev2Warps, st>>>(
+              P, c->use_cuaev ? 1 : 0, d_x4.as<V4>(), d_beg.as<int64_t>(), d_cnt.as<int>(), d_jlist.as<int>(), d_order.as<int>(),
+              nlocal, rows, ld_aev, hi, lo, ldp, plane_mode, f16::kScaleAev, cap1, capA1, L1.bytes, d_err.as<int>(), rs);
+          c->launches++;
+          rs = Aev2Rows();
+          rs.sel_cnt = d_ovf.as<int>() + 2; rs.sel_rows = d_ovf_rows.as<int>();
+        }
+        if (two_pass) {
+          ANIB_CUDA_OK(cudaFuncSetAttribute(kern_strided, cudaFuncAttributeMaxDynamicSharedMemorySize, smem2));
+          kern_strided<<<std::min(grid, 592), kAev2Warps * 32, smem2, st>>>(
+              P, c->use_cuaev ? 1 : 0, d_x4.as<V4>(), d_beg.as<int64_t>(), d_cnt.as<int>(), d_jlist.as<int>(), d_order.as<int>(),
+              nlocal, rows, ld_aev, hi, lo, ldp, plane_mode, f16::kScaleAev, cap, capA, L2.bytes, d_err.as<int>(), rs);
+        } else
+          kern<<<grid, kAev2Warps * 32, smem2, st>>>(
+              P, c->use_cuaev ? 1 : 0, d_x4.as<V4>(), d_beg.as<int64_t>(), d_cnt.as<int>(), d_jlist.as<int>(), d_order.as<int>(),
+              nlocal, rows, ld_aev, hi, lo, ldp, plane_mode, f16::kScaleAev, cap, capA, L2.bytes, d_err.as<int>(), rs);
         return 0;
       };
       int rc2 = 0;
-      if (aev_gen == 2 && P.nZ == 4 && P.nA == 8) rc2 = launch2(aev2_forward_kernel<T, 4, 8>);
-      else if (aev_gen == 2 && P.nZ == 8 && P.nA == 4) rc2 = launch2(aev2_forward_kernel<T, 8, 4>);
-      else if (aev_gen == 2 && P.nZ == 8 && P.nA == 8) rc2 = launch2(aev2_forward_kernel<T, 8, 8>);
+      if (aev_gen == 2 && P.nZ == 4 && P.nA == 8) rc2 = launch2(aev2_forward_kernel<T, 4, 8>, aev2_forward_kernel<T, 4, 8, true>);
+      else if (aev_gen == 2 && P.nZ == 8 && P.nA == 4) rc2 = launch2(aev2_forward_kernel<T, 8, 4>, aev2_forward_kernel<T, 8, 4, true>);
+      else if (aev_gen == 2 && P.nZ == 8 && P.nA == 8) rc2 = launch2(aev2_forward_kernel<T, 8, 8>, aev2_forward_kernel<T, 8, 8, true>);
       else
         aev_forward_kernel<T><<<(nlocal + kAevWarps - 1) / kAevWarps, kAevWarps * 32, smem, st>>>(
             P, c->use_cuaev ? 1 : 0, d_x4.as<V4>(), d_beg.as<int64_t>(), d_cnt.as<int>(), d_jlist.as<int>(),
@@ -615,21 +655,41 @@ struct Engine : EngineBase {
         c->launches++;
         return 0;
       };
-      auto launch2 = [&](auto kern) -> int {
+      auto launch2 = [&](auto kern, auto kern_strided) -> int {
         const Aev2Layout L2 = aev2_layout<T>(cap, capA, acc_b, P.nZ, P.nA, true);
         const int smem2 = L2.bytes * kAev2Warps;
         ANIB_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem2));
-        kern<<<(nlocal + kAev2Warps - 1) / kAev2Warps, kAev2Warps * 32, smem2, st>>>(
-            P, c->use_cuaev ? 1 : 0, d_x4.as<V4>(), d_beg.as<int64_t>(), d_cnt.as<int>(), d_jlist.as<int>(), d_order.as<int>(),
-            nlocal, d_daev.as<T>(), ld_aev, d_force.as<T>(), want_virial ? d_virial.as<double>() : nullptr,
-            (T)kHartree2KcalMol, cap, capA, L2.bytes);
+        const int grid = (nlocal + kAev2Warps - 1) / kAev2Warps;
+        Aev2Rows rs;
+        if (two_pass) {
+          const Aev2Layout L1 = aev2_layout<T>(cap1, capA1, acc_b, P.nZ, P.nA, true);
+          rs.ovf_cnt = d_ovf.as<int>() + 3; rs.ovf_rows = d_ovf_rows.as<int>() + nlocal;
+          kern<<<grid, kAev2Warps * 32, L1.bytes * kAev2Warps, st>>>(
+              P, c->use_cuaev ? 1 : 0, d_x4.as<V4>(), d_beg.as<int64_t>(), d_cnt.as<int>(), d_jlist.as<int>(), d_order.as<int>(),
+              nlocal, d_daev.as<T>(), ld_aev, d_force.as<T>(), want_virial ? d_virial.as<double>() : nullptr,
+              (T)kHartree2KcalMol, cap1, capA1, L1.bytes, rs);
+          c->launches++;
+          rs = Aev2Rows();
+          rs.sel_cnt = d_ovf.as<int>() + 3; rs.sel_rows = d_ovf_rows.as<int>() + nlocal;
+        }
+        if (two_pass) {
+          ANIB_CUDA_OK(cudaFuncSetAttribute(kern_strided, cudaFuncAttributeMaxDynamicSharedMemorySize, smem2));
+          kern_strided<<<std::min(grid, 592), kAev2Warps * 32, smem2, st>>>(
+              P, c->use_cuaev ? 1 : 0, d_x4.as<V4>(), d_beg.as<int64_t>(), d_cnt.as<int>(), d_jlist.as<int>(), d_order.as<int>(),
+              nlocal, d_daev.as<T>(), ld_aev, d_force.as<T>(), want_virial ? d_virial.as<double>() : nullptr,
+              (T)kHartree2KcalMol, cap, capA, L2.bytes, rs);
+        } else
+          kern<<<grid, kAev2Warps * 32, smem2, st>>>(
+              P, c->use_cuaev ? 1 : 0, d_x4.as<V4>(), d_beg.as<int64_t>(), d_cnt.as<int>(), d_jlist.as<int>(), d_order.as<int>(),
+              nlocal, d_daev.as<T>(), ld_aev, d_force.as<T>(), want_virial ? d_virial.as<double>() : nullptr,
+              (T)kHartree2KcalMol, cap, capA, L2.bytes, rs);
         c->launches++;
         return 0;
       };
       int rc;
-      if (aev_gen == 2 && P.nZ == 4 && P.nA == 8) rc = launch2(aev2_backward_kernel<T, 4, 8>);
-      else if (aev_gen == 2 && P.nZ == 8 && P.nA == 4) rc = launch2(aev2_backward_kernel<T, 8, 4>);
-      else if (aev_gen == 2 && P.nZ == 8 && P.nA == 8) rc = launch2(aev2_backward_kernel<T, 8, 8>);
+      if (aev_gen == 2 && P.nZ == 4 && P.nA == 8) rc = launch2(aev2_backward_kernel<T, 4, 8>, aev2_backward_kernel<T, 4, 8, true>);
+      else if (aev_gen == 2 && P.nZ == 8 && P.nA == 4) rc = launch2(aev2_backward_kernel<T, 8, 4>, aev2_backward_kernel<T, 8, 4, true>);
+      else if (aev_gen == 2 && P.nZ == 8 && P.nA == 8) rc = launch2(aev2_backward_kernel<T, 8, 8>, aev2_backward_kernel<T, 8, 8, true>);
       else if (P.nZ == 4) rc = launch(aev_backward_kernel<T, 4>);
       else if (P.nZ == 8) rc = launch(aev_backward_kernel<T, 8>);
       else if (P.nZ == 1) rc = launch(aev_backward_kernel<T, 1>);
@@ -665,16 +725,15 @@ struct Engine : EngineBase {
       c->launches++;
     }
     // ---- D2H
-    const size_t small_bytes = (1 + 1 + kVirialSlots * 9) * sizeof(double);
-    ANIB_RESERVE(h_small, small_bytes);
-    double* hs = h_small.as<double>();
     bool need_sync = false;
     if (want_e) { ANIB_CUDA_OK(cudaMemcpyAsync(hs, d_scalars.p, sizeof(double), cudaMemcpyDeviceToHost, st)); need_sync = true; }
     if (want_virial) {
-      ANIB_CUDA_OK(cudaMemcpyAsync(hs + 2, d_virial.p, kVirialSlots * 9 * sizeof(double), cudaMemcpyDeviceToHost, st));
+      ANIB_CUDA_OK(cudaMemcpyAsync(hs + 4, d_virial.p, kVirialSlots * 9 * sizeof(double), cudaMemcpyDeviceToHost, st));
       need_sync = true;
     }
     ANIB_CUDA_OK(cudaMemcpyAsync(hs + 1, d_err.p, sizeof(int), cudaMemcpyDeviceToHost, st));
+    ANIB_CUDA_OK(cudaMemcpyAsync(hs + 2, d_ovf.p, 4 * sizeof(int), cudaMemcpyDeviceToHost, st));
+    stats_pending = true;
     f_direct = false;
     if (out_force_host != nullptr && ntotal > 0 && pin_f.ensure(out_force_host, (size_t)ntotal * 3 * sizeof(double))) {
       // widen on the device, DMA straight into the caller's array
@@ -708,7 +767,7 @@ struct Engine : EngineBase {
     if (want_virial) {
       double w[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
       for (int sl = 0; sl < kVirialSlots; sl++)
-        for (int q = 0; q < 9; q++) w[q] += hs[2 + sl * 9 + q];
+        for (int q = 0; q < 9; q++) w[q] += hs[4 + sl * 9 + q];
       for (int a = 0; a < 3; a++)
         for (int b = 0; b < 3; b++) out_virial9[3 * a + b] = 0.5 * (w[3 * a + b] + w[3 * b + a]);
     }

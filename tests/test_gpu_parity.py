@@ -221,6 +221,28 @@ def test_stable_caller_buffers_are_pinned_in_place(ANI, ani2x_synth_path):
     assert abs(e1 - e2) <= 1e-9 * abs(e2) and np.abs(fs - f2).max() <= 1e-4 and abs(e1 - e0) > 1e-6
 
 
+@pytest.mark.parametrize("single", [False, True])
+def test_two_pass_aev_defers_rows_that_outgrow_their_buffers(ANI, ani2x_synth_path, single):
+    """The AEV kernels size their first-pass shared-memory buffers from the survivor counts of the previous steps and hand a row
+    that does not fit to a second pass with list-sized buffers.  Here the SAME list is first used on an expanded geometry (few
+    neighbours inside Rcr / Rca -> small buffers), then on the original one (every atom outgrows them): energies, forces and
+    virial must equal those of a fresh context, whose first call is single-pass."""
+    x, sp, box = domain.make_water_box((6, 6, 5), seed=21)
+    sub, il, nn, jl = periodic_system(x, sp, box)
+    ani = ANI(ani2x_synth_path, 0, -1, True, True, single)
+    far = sub.x * 1.35                                     # every pair inside 5.1 A here is inside 3.8 A there: still listed
+    ani.compute(sub.species, far, il, jl, nn, nlocal=sub.nlocal, ago=0)
+    for _ in range(2):
+        ani.compute(None, far, nlocal=sub.nlocal, ago=1)
+    e, f, _, v = ani.compute(None, sub.x, nlocal=sub.nlocal, ago=1, vflag=True)
+    fresh = ANI(ani2x_synth_path, 0, -1, True, True, single)
+    e0, f0, _, v0 = fresh.compute(sub.species, sub.x, il, jl, nn, nlocal=sub.nlocal, ago=0, vflag=True)
+    tol = 1e-4 if single else 1e-9
+    assert abs(e - e0) <= 1e-9 * abs(e0) and np.abs(f - f0).max() <= tol and np.abs(v - v0).max() <= 1e-3 * max(1.0, np.abs(v0).max())
+    e1, f1, _, _ = ani.compute(None, sub.x, nlocal=sub.nlocal, ago=1)          # buffers have caught up: no deferred rows now
+    assert abs(e1 - e0) <= 1e-9 * abs(e0) and np.abs(f1 - f0).max() <= tol
+
+
 def test_error_paths(ANI, ani1xnr_path, water30):
     ani = ANI(ani1xnr_path, 0)
     sp = water30["species"].copy()
