@@ -229,7 +229,9 @@ aev2_forward_row(const AevConst<T>& P, int radial_filter, const typename Vec4T<T
         const int ntri = (s == t) ? ns * (ns - 1) / 2 : ns * nt;
         if (ntri == 0) continue;
         T accr = T(0);
-        int ta = 0, rem = lane;                       // triangular enumeration state (s == t)
+        // index decode without integer division: floor((idx + 0.5) / d) in fp32 is exact here (idx < 2^13, d <= capA)
+        const float inv_ns = 1.0f / (float)ns, inv_nt = 1.0f / (float)nt;
+        const int nfull = ns * ((ns - 1) / 2);        // s == t: triples on the complete wrapped diagonals (a, (a+k+1) mod ns)
         for (int t0 = 0; t0 < ntri; t0 += 32) {
           const int idx = t0 + lane;
           T f1[NZ], f2[NA];
@@ -240,11 +242,14 @@ aev2_forward_row(const AevConst<T>& P, int radial_filter, const typename Vec4T<T
           if (idx < ntri) {
             int a, b;
             if (s == t) {
-              while (rem >= ns - 1 - ta) { rem -= ns - 1 - ta; ta++; }
-              a = as0 + ta; b = a + 1 + rem;
-              rem += 32;
+              int ta, tb;
+              if (idx < nfull) {
+                const int k = __float2int_rd(((float)idx + 0.5f) * inv_ns);
+                ta = idx - k * ns; tb = ta + k + 1; if (tb >= ns) tb -= ns;
+              } else { ta = idx - nfull; tb = ta + ns / 2; }
+              a = as0 + ta; b = as0 + tb;
             } else {
-              const int qa = idx / nt;
+              const int qa = __float2int_rd(((float)idx + 0.5f) * inv_nt);
               a = as0 + qa; b = at0 + (idx - qa * nt);
             }
             const V4 A = sh_a[a], B = sh_a[b];
@@ -472,9 +477,10 @@ aev2_backward_row(const AevConst<T>& P, int radial_filter, const typename Vec4T<
   {
     const int ntri = na * (na - 1) / 2;
     const int nfull = na * ((na - 1) / 2);        // triples on the complete diagonals (all of them when na is odd)
+    const float inv_na = 1.0f / (float)max(na, 1);   // floor((t + 0.5) / na) in fp32 is exact for t < 2^13: no integer division
     for (int t = lane; t < ntri; t += 32) {
       int a, b;
-      if (t < nfull) { const int k = t / na; a = t - k * na; b = a + k + 1; if (b >= na) b -= na; }
+      if (t < nfull) { const int k = __float2int_rd(((float)t + 0.5f) * inv_na); a = t - k * na; b = a + k + 1; if (b >= na) b -= na; }
       else { a = t - nfull; b = a + na / 2; }
       const V4 A = sh_a[a], B = sh_a[b];
       const T fca = sh_afc[a], fcb = sh_afc[b];
