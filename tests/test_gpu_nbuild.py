@@ -52,3 +52,30 @@ def test_step_on_device_built_list(ani2x_synth_path):
     e1, f1, _, _ = ani.compute(None, sub.x, nlocal=sub.nlocal, ago=1)
     assert abs(e1 - e0) <= 1e-7 * abs(e0)
     assert np.abs(f1 - f0).max() <= 1e-4        # same sets, different order inside a row: fp32 summation order only
+
+
+def test_rebuild_after_caller_array_grew_in_place(ani2x_synth_path):
+    """What `pair_style ani ... device` does under LAMMPS: atom->x is page-locked in place by ani_compute once it is stable; at a
+    later rebuild the same allocation holds MORE atoms (ghosts grew, realloc extended in place), so the host copy of the
+    rebuild spans memory beyond the registered range.  The library must drop the stale page-lock first (it used to fail with
+    `invalid argument`), and ani_ctx_release_host_buffers must be harmless at any time."""
+    x, sp, box = domain.make_water_box((5, 5, 5), seed=77)
+    sub = domain.decompose(x, sp, box)[0]
+    nt = sub.x.shape[0]
+    n1 = sub.nlocal + (nt - sub.nlocal) // 2                        # first: only half of the ghosts are there
+    arena = np.zeros((nt + 64, 3))                                  # the caller's allocation, larger than its contents
+    arena[:nt] = sub.x
+    f = np.zeros((nt + 64, 3))
+    ani = runner.ANI(ani2x_synth_path, 0, -1, True, True, True)
+    ani.build_neighbors(sub.species[:n1], arena[:n1], sub.nlocal, 7.1)
+    for _ in range(4):                                              # arena[:n1] becomes page-locked in place
+        ani.compute(None, arena[:n1], nlocal=sub.nlocal, ago=1, out_force=f[:n1])
+    P = ani.build_neighbors(sub.species, arena[:nt], sub.nlocal, 7.1)   # same pointer, more bytes
+    e, fo, _, _ = ani.compute(None, arena[:nt], nlocal=sub.nlocal, ago=1, out_force=f[:nt])
+    fresh = runner.ANI(ani2x_synth_path, 0, -1, True, True, True)
+    assert fresh.build_neighbors(sub.species, sub.x, sub.nlocal, 7.1) == P
+    e0, f0, _, _ = fresh.compute(None, sub.x, nlocal=sub.nlocal, ago=1)
+    assert abs(e - e0) <= 1e-9 * abs(e0) and np.abs(fo - f0).max() <= 1e-4
+    assert ani._L.ani_ctx_release_host_buffers(ani._ctx) == 0
+    e2, f2, _, _ = ani.compute(None, arena[:nt], nlocal=sub.nlocal, ago=1, out_force=f[:nt])
+    assert abs(e2 - e0) <= 1e-9 * abs(e0) and np.abs(f2 - f0).max() <= 1e-4
