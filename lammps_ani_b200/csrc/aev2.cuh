@@ -23,7 +23,7 @@ constexpr int kAev2TS = 36;
 
 struct Aev2Layout {
   int off_r, off_rfc, off_s, off_a, off_afc, off_as, off_acc, off_f1, off_f2, off_ud, off_us, off_seg;   // forward
-  int off_d, off_j, off_adfc, off_ai, off_g;                                                              // backward extras
+  int off_d, off_j, off_adfc, off_ai, off_g, off_gi;                                                      // backward extras
   int bytes;
 };
 
@@ -55,6 +55,7 @@ __host__ __device__ inline Aev2Layout aev2_layout(int cap, int capA, int acc_ele
     L.off_adfc = take(capA * ts, 8);
     L.off_ai = take(capA * 4, 4);
     L.off_g = take(cap * 3 * ts, 8);
+    L.off_gi = take(ts == 4 ? capA * 6 * 4 : 0, 8);   // fp32: fixed-point accumulators of the angular gradients (hi[3], lo[3])
     L.off_j = take(cap * 4, 4);
     L.off_s = take(cap * 4, 4);
   }
@@ -373,6 +374,7 @@ aev2_backward_row(const AevConst<T>& P, int radial_filter, const typename Vec4T<
   int* sh_j = (int*)(base + L.off_j);
   int* sh_as = (int*)(base + L.off_as);
   int* sh_ai = (int*)(base + L.off_ai);
+  int* sh_gi = (int*)(base + L.off_gi);
 
   const int i = order[row];
   const V4 xi = x4[i];
@@ -456,6 +458,12 @@ aev2_backward_row(const AevConst<T>& P, int radial_filter, const typename Vec4T<
     if (n > cap) n = cap;
   }
 
+  // fp32: the per-neighbour angular gradients are summed in 2^-36 fixed point, split into two int32 words (q = hi * 2^24 + lo,
+  // lo in [0, 2^24)): shared-memory integer adds are native, float adds are compare-and-swap loops; a neighbour receives at most
+  // na - 1 <= 95 contributions, so neither word overflows for |term| < 5000, and the sum does not depend on the order
+  constexpr bool kFixed = sizeof(T) == 4;
+  if (kFixed)
+    for (int e = lane; e < na * 6; e += 32) sh_gi[e] = 0;
   // ---- radial: lane = neighbour
   for (int e = lane; e < n; e += 32) {
     const V4 d = sh_d[e];
@@ -518,16 +526,37 @@ aev2_backward_row(const AevConst<T>& P, int radial_filter, const typename Vec4T<
       const T dE_drb = T(2) * fca * sh_adfc[b] * S0 + half_s1;
       const T dE_dcos = T(2) * fca * fcb * T(0.95) * S2;
       const T ka = dE_dcos / A.w, kb = dE_dcos / B.w;
-      const int ea = sh_ai[a], eb = sh_ai[b];
-      atomicAdd(sh_g + 3 * ea + 0, dE_dra * A.x + ka * (B.x - cosv * A.x));
-      atomicAdd(sh_g + 3 * ea + 1, dE_dra * A.y + ka * (B.y - cosv * A.y));
-      atomicAdd(sh_g + 3 * ea + 2, dE_dra * A.z + ka * (B.z - cosv * A.z));
-      atomicAdd(sh_g + 3 * eb + 0, dE_drb * B.x + kb * (A.x - cosv * B.x));
-      atomicAdd(sh_g + 3 * eb + 1, dE_drb * B.y + kb * (A.y - cosv * B.y));
-      atomicAdd(sh_g + 3 * eb + 2, dE_drb * B.z + kb * (A.z - cosv * B.z));
+      const T gax = dE_dra * A.x + ka * (B.x - cosv * A.x), gay = dE_dra * A.y + ka * (B.y - cosv * A.y),
+              gaz = dE_dra * A.z + ka * (B.z - cosv * A.z);
+      const T gbx = dE_drb * B.x + kb * (A.x - cosv * B.x), gby = dE_drb * B.y + kb * (A.y - cosv * B.y),
+              gbz = dE_drb * B.z + kb * (A.z - cosv * B.z);
+      if (kFixed) {
+        auto fx_add = [&](int word, T v) {
+          const long long q = __float2ll_rn((float)v * 68719476736.0f);          // 2^36
+          atomicAdd(sh_gi + word, (int)(q >> 24));
+          atomicAdd(sh_gi + word + 3, (int)(q & 0xFFFFFF));
+        };
+        fx_add(6 * a + 0, gax); fx_add(6 * a + 1, gay); fx_add(6 * a + 2, gaz);
+        fx_add(6 * b + 0, gbx); fx_add(6 * b + 1, gby); fx_add(6 * b + 2, gbz);
+      } else {
+        const int ea = sh_ai[a], eb = sh_ai[b];
+        atomicAdd(sh_g + 3 * ea + 0, gax); atomicAdd(sh_g + 3 * ea + 1, gay); atomicAdd(sh_g + 3 * ea + 2, gaz);
+        atomicAdd(sh_g + 3 * eb + 0, gbx); atomicAdd(sh_g + 3 * eb + 1, gby); atomicAdd(sh_g + 3 * eb + 2, gbz);
+      }
     }
   }
   __syncwarp();
+  if (kFixed) {   // fold the fixed-point sums into the per-neighbour gradients (one angular slot per neighbour: no conflicts)
+    for (int a = lane; a < na; a += 32) {
+      const int ea = sh_ai[a];
+#pragma unroll
+      for (int q = 0; q < 3; q++) {
+        const long long v = ((long long)sh_gi[6 * a + q] << 24) + (long long)sh_gi[6 * a + 3 + q];
+        sh_g[3 * ea + q] += (T)(__ll2float_rn(v) * 1.4551915228366852e-11f);   // 2^-36
+      }
+    }
+    __syncwarp();
+  }
   // ---- scatter: F_j -= g, F_i += sum g, virial -= g (x) d
   T fix = T(0), fiy = T(0), fiz = T(0);
   double vir[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
