@@ -236,13 +236,16 @@ void PairANIB200::compute(int eflag, int vflag) {
     eat = out_eatom.data();
   }
   const double* xflat = ntotal > 0 ? &x[0][0] : out_force.data();   // atom->x rows are contiguous (memory->create)
-  if (ani_compute(ctx, xflat, &energy, out_force.data(), eat, vflag_either ? vir9 : nullptr)) fail("evaluation failed");
+  if (ani_compute(ctx, xflat, eflag_global ? &energy : nullptr, out_force.data(), eat, vflag_either ? vir9 : nullptr))
+    fail("evaluation failed");
 
   // newton off on both flags: Verlet does not reverse-communicate, so fold ghost forces here, on out_force and
   // not on f whose ghost entries are stale (pair_ani.cpp:192-201)
   if (!force->newton) comm->reverse_comm(this);
 
-  for (int i = 0; i < ntotal; i++) {
+  // with newton off the ghost entries of f are never read again (their share was folded onto the owners just above)
+  const int nf = force->newton ? ntotal : nlocal;
+  for (int i = 0; i < nf; i++) {
     f[i][0] += out_force[3 * (size_t)i + 0];
     f[i][1] += out_force[3 * (size_t)i + 1];
     f[i][2] += out_force[3 * (size_t)i + 2];
