@@ -262,6 +262,7 @@ def main():
     # ani_compute): HOST x[ntotal] in, HOST f[ntotal] + energy out, H2D / D2H inside the timed region every step
     x_all = np.ascontiguousarray(sub.x, dtype=np.float64)
     f_host = np.empty((ntotal, 3), dtype=np.float64)     # the pair style's persistent out_force vector (pair_ani.cpp:89-95)
+    ani.set_option("pin_user", 1)                         # both arrays live until release_host_buffers() below, as in the pair style
     for _ in range(3):
         ani.compute(sub.species, x_all, nlocal=nlocal, ago=1, out_force=f_host)
     barrier()
@@ -273,6 +274,8 @@ def main():
     g1.record()
     barrier()
     ms_e2e = g0.elapsed_time(g1)
+    ani.release_host_buffers()
+    ani.set_option("pin_user", 0)
     clocks = sampler.stop()
     # ---------------- per-stage device times (library CUDA events on the same stream), a few extra steps
     ani.enable_timing(True)

@@ -60,7 +60,17 @@ int ani_ctx_set_mlp_mode(ani_ctx* ctx, int mode); /* enum ani_mlp_mode; single p
  * ani_ctx_reset_stream goes back to the context's own non-blocking stream. */
 int ani_ctx_set_stream(ani_ctx* ctx, void* cuda_stream);
 int ani_ctx_reset_stream(ani_ctx* ctx);
+/* Waits for the context's stream AND reports (once) any device-side error flag a step that was not synchronised raised:
+ * 2 = more angular neighbours than the kernels hold, 3 = an MLP value left the fp16 operand range of the f16x3 path.  */
 int ani_ctx_synchronize(ani_ctx* ctx);
+/* Per-context switches (the reference has only LAMMPS_ANI_ALLOW_TF32 / LAMMPS_ANI_PROFILING, ani.cpp:41, pair_ani.cpp:49).
+ * "mlp_fused" 1 (default): the f16x3 MLP of a species bucket runs as one fused kernel, 0: layer by layer;
+ * "pin_user" 1 (default 0): page-lock caller x / out_force arrays seen at a stable address and DMA from / to them
+ * directly -- the caller then must call ani_ctx_release_host_buffers before freeing or reallocating them (pair style, bench);
+ * "aev_two_pass" 1 (default) / 0; "gemm_ctas" n > 0: cap the persistent GEMM grids at n CTAs; "fused_prof" 1: print the
+ * fused kernel's cycle counters to stderr.  The environment (ANI_B200_FUSED, ANI_B200_AEV_TWO_PASS, ANI_B200_GEMM_CTAS,
+ * ANI_B200_FUSED_PROF) only sets the defaults a context starts with. */
+int ani_ctx_set_option(ani_ctx* ctx, const char* name, int value);
 
 /* ---- neighbour data: call when the list was rebuilt (neighbor->ago == 0, pair_ani.cpp:107-151) ---------
  * species[ntotal] = LAMMPS type-1 for local AND ghost atoms (pair_ani.cpp:109-111).
@@ -91,8 +101,8 @@ int ani_set_neighbors_table(ani_ctx* ctx, int nlocal, int ntotal, const int* typ
  * border cells, which keeps the result correct and only costs time.  npairs_out (optional): stored pairs. */
 int ani_build_neighbors(ani_ctx* ctx, int nlocal, int ntotal, const int* species, const double* x, int x_on_device,
                         double cutoff, const double lo[3], const double hi[3], int64_t* npairs_out);
-/* Drop the page-locks the library took on caller buffers (ani_compute page-locks an x / out_force array it sees at a stable
- * address).  Call it BEFORE freeing or reallocating such a buffer (the pair style does when atom->nmax or its out_force vector
+/* Drop the page-locks the library took on caller buffers (with option "pin_user" 1, ani_compute page-locks an x / out_force
+ * array it sees at a stable address).  Call it BEFORE freeing or reallocating such a buffer (the pair style does when atom->nmax or its out_force vector
  * grows); harmless otherwise. */
 int ani_ctx_release_host_buffers(ani_ctx* ctx);
 /* Copy the installed full list to host memory: numneigh [nlocal], jlist [npairs] in atom order (tests). */

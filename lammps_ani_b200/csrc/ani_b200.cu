@@ -18,8 +18,7 @@
 #include "misc.cuh"
 #include "mlp_simt.cuh"
 #include "mlp_f16.cuh"
-#include "mlp_f16_multi.cuh"
-#include "mlp_f16_chain.cuh"
+#include "mlp_f16_fused.cuh"
 #include "mlp_tc.cuh"
 #include "nbuild.cuh"
 
@@ -80,14 +79,17 @@ struct PinnedBuf {
     }                                                                                                         \
   } while (0)
 
-// A caller buffer (LAMMPS's x / the pair style's force vector) that was seen at the same address on consecutive calls is
-// page-locked in place (cudaHostRegister) so the H2D / D2H copies go straight from / to it: no staging memcpy, no host
-// conversion loop.  Buffers that move every call keep the pinned-staging path.  ANI_B200_PIN_USER=0 disables.
+// OPT-IN (option "pin_user" 1; the pair style and bench.py set it): a caller buffer (LAMMPS's x / the pair style's force
+// vector) that was seen at the same address on consecutive calls is page-locked in place (cudaHostRegister) so the H2D / D2H
+// copies go straight from / to it: no staging memcpy, no host conversion loop.  The caller then owes the library an
+// ani_ctx_release_host_buffers() before it frees or reallocates such a buffer (a new allocation at the same address would
+// otherwise inherit a stale registration).  Off by default: generic callers get the pinned-staging path, which has no such
+// contract.
 struct UserPin {
   const void* p = nullptr; size_t bytes = 0; bool registered = false, foreign = false; int seen = 0;
-  bool ensure(const void* q, size_t n) {
-    static const bool enabled = !(getenv("ANI_B200_PIN_USER") && atoi(getenv("ANI_B200_PIN_USER")) == 0);
-    if (!enabled || q == nullptr || n == 0) return false;
+  bool ensure(const void* q, size_t n, bool enabled) {
+    if (!enabled) { if (p) release(); return false; }
+    if (q == nullptr || n == 0) return false;
     if (q == p && (registered || foreign) && n <= bytes) return true;   // ghost counts shrink and grow between rebuilds
     if (q == p && n == bytes) {
       if (++seen < 2) return false;
@@ -119,6 +121,7 @@ struct EngineBase {
                               const double* lo, const double* hi, int64_t* npairs_out) = 0;
   virtual int get_neighbors(int* numneigh, int* jlist) = 0;
   virtual void release_pins() = 0;
+  virtual int check_errors() = 0;
 };
 
 template <typename T>
@@ -147,6 +150,8 @@ struct ani_ctx {
   int mlp_mode = ANI_MLP_FP32_SIMT;
   cudaStream_t stream = nullptr, own_stream = nullptr;
   bool timing = false;
+  // per-context switches (ani_ctx_set_option; the environment only provides their defaults at creation)
+  int opt_mlp_fused = 1, opt_fused_prof = 0, opt_gemm_ctas = 0, opt_aev_two_pass = 1, opt_pin_user = 0;
   cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
   float stage_ms[5] = {0, 0, 0, 0, 0};
   int launches = 0;
@@ -183,7 +188,7 @@ struct Engine : EngineBase {
   DevBuf d_H, d_D, d_G;   // MLP intermediates of one chunk
   TcWork tcw;
   f16::Work hwork;
-  std::vector<f16::Work> hring;   // work sets of the chunks in flight in the pipelined MLP
+  f16::FusedWork fwork;
   int64_t ld_planes = 0;   // row pitch of the fp16 AEV planes (multiple of 8 halves = 16 bytes for TMA)
   PinnedBuf h_x, h_f, h_small;
   UserPin pin_x, pin_f;
@@ -230,8 +235,8 @@ struct Engine : EngineBase {
       for (int t = s; t < hm.S; t++) { P.triu[s][t] = p; P.triu[t][s] = p; p++; }
     Pfull = P;
     nets.resize(hm.S);
-    ANIB_RESERVE(d_err, sizeof(int));
-    ANIB_CUDA_OK(cudaMemset(d_err.p, 0, sizeof(int)));
+    ANIB_RESERVE(d_err, 2 * sizeof(int));   // [0] angular-neighbour overflow, [1] fp16 operand range (mlp_f16_fused.cuh)
+    ANIB_CUDA_OK(cudaMemset(d_err.p, 0, 2 * sizeof(int)));
     ANIB_RESERVE(d_scalars, 16 * sizeof(double));
     ANIB_RESERVE(d_virial, kVirialSlots * 9 * sizeof(double));
     ANIB_RESERVE(d_partial, 1024 * sizeof(double));
@@ -527,7 +532,7 @@ struct Engine : EngineBase {
     const void* xsrc = x;
     if (!x_on_device) {
       const size_t bytes = (size_t)ntotal * 3 * sizeof(double);
-      if (pin_x.ensure(x, bytes)) {
+      if (pin_x.ensure(x, bytes, c->opt_pin_user != 0)) {
         ANIB_CUDA_OK(cudaMemcpyAsync(d_xraw.p, x, bytes, cudaMemcpyHostToDevice, st));   // DMA straight from the caller's array
       } else {
         ANIB_RESERVE(h_x, bytes);
@@ -552,13 +557,15 @@ struct Engine : EngineBase {
     ANIB_RESERVE(h_small, small_bytes);
     double* hs = h_small.as<double>();
     if (!stats_pending) memset(hs, 0, small_bytes);
+    // flags raised by a step that was not synchronised (device-resident callers) surface here, one call late at most
+    if (stats_pending) if (int rc = check_errors()) return rc;
     if (stats_pending) {
       const int* hst = (const int*)(hs + 2);
       const int mn = hst[0], mna = hst[1];
       if (mn > 0) cap_fit = (mn + std::max(4, mn / 8) + 7) / 8 * 8;
       if (mn > 0) capA_fit = (mna + std::max(4, mna / 8) + 7) / 8 * 8;
     }
-    static const bool two_pass_on = f16::env_int("ANI_B200_AEV_TWO_PASS", 1) != 0;
+    const bool two_pass_on = c->opt_aev_two_pass != 0;
     const int cap1 = std::min(cap, cap_fit), capA1 = std::min(capA, std::max(capA_fit, 8));
     const bool two_pass = two_pass_on && aev_gen == 2 && cap_fit > 0 && nlocal > 0 && (cap1 + 16 <= cap || capA1 + 16 <= capA);
     ANIB_RESERVE(d_ovf, 4 * sizeof(int));
@@ -731,11 +738,11 @@ struct Engine : EngineBase {
       ANIB_CUDA_OK(cudaMemcpyAsync(hs + 4, d_virial.p, kVirialSlots * 9 * sizeof(double), cudaMemcpyDeviceToHost, st));
       need_sync = true;
     }
-    ANIB_CUDA_OK(cudaMemcpyAsync(hs + 1, d_err.p, sizeof(int), cudaMemcpyDeviceToHost, st));
+    ANIB_CUDA_OK(cudaMemcpyAsync(hs + 1, d_err.p, 2 * sizeof(int), cudaMemcpyDeviceToHost, st));
     ANIB_CUDA_OK(cudaMemcpyAsync(hs + 2, d_ovf.p, 4 * sizeof(int), cudaMemcpyDeviceToHost, st));
     stats_pending = true;
     f_direct = false;
-    if (out_force_host != nullptr && ntotal > 0 && pin_f.ensure(out_force_host, (size_t)ntotal * 3 * sizeof(double))) {
+    if (out_force_host != nullptr && ntotal > 0 && pin_f.ensure(out_force_host, (size_t)ntotal * 3 * sizeof(double), c->opt_pin_user != 0)) {
       // widen on the device, DMA straight into the caller's array
       const int64_t n3 = (int64_t)ntotal * 3;
       ANIB_RESERVE(d_fout, (size_t)n3 * sizeof(double));
@@ -759,8 +766,7 @@ struct Engine : EngineBase {
     if (tm) { cudaEventRecord(c->ev[5], st); need_sync = true; }
     if (need_sync) {
       ANIB_CUDA_OK(cudaStreamSynchronize(st));
-      int err = *(int*)(hs + 1);
-      if (err) { set_error("an atom has more than " + std::to_string(capA) + " neighbours inside the angular cutoff"); return 2; }
+      if (int rc = check_errors()) return rc;
     }
     ANIB_CUDA_OK(cudaGetLastError());
     if (want_e) *out_energy = hs[0];
@@ -781,6 +787,20 @@ struct Engine : EngineBase {
     return 0;
   }
   PinnedBuf h_eat;
+
+  // Device-side error flags of the last finished step (copied to pinned memory by every step): report once, then clear.
+  int check_errors() override {
+    if (!h_small.p) return 0;
+    int* herr = (int*)(h_small.as<double>() + 1);
+    const int e0 = herr[0], e1 = herr[1];
+    if (!e0 && !e1) return 0;
+    herr[0] = herr[1] = 0;
+    cudaMemsetAsync(d_err.p, 0, 2 * sizeof(int), c->stream);
+    if (e0) { set_error("an atom has more than " + std::to_string(capA) + " neighbours inside the angular cutoff"); return 2; }
+    set_error("an MLP activation or gradient left the fp16 operand range of the f16x3 tensor-core path (|16 h| or |256 g| >= 65504): "
+              "the result of this step is invalid; use ani_ctx_set_mlp_mode(ANI_MLP_TF32X3 or ANI_MLP_FP32_SIMT) for this system");
+    return 3;
+  }
 
   // test hook: rows back in atom order and in the FULL AEV layout (dropped columns are zero)
   int get_aev(double* aev, double* daev) override {
@@ -832,13 +852,17 @@ template <> int Engine<double>::mlp_f16_species(int, int, int) {
 }
 
 template <> int Engine<float>::mlp_f16_species(int s, int row0, int R) {
-  g_dbg_word_fn = f16::chain_dbg_word;
-  static const int chain = f16::env_int("ANI_B200_CHAIN", 0);   // 1: chained-layer kernels (mlp_f16_chain.cuh): correct, not yet faster
-  if (chain && f16::chain_supported(nets[s].dims))
-    return f16::mlp_species_chain(c->stream, nets[s].hw, hwork, M, nets[s].dims, (const __half*)d_aev_hi.p, (const __half*)d_aev_lo.p,
+  g_dbg_word_fn = f16::fused_dbg_word;
+  // default: the whole network of a bucket in one kernel (mlp_f16_fused.cuh); option "mlp_fused" 0 = layer by layer (mlp_f16.cuh)
+  if (c->opt_mlp_fused && f16::fused_supported(nets[s].dims)) {
+    f16::FusedOptions fo;
+    fo.flag = d_err.as<int>() + 1; fo.prof = c->opt_fused_prof; fo.cta_cap = c->opt_gemm_ctas;
+    ANIB_CUDA_OK(cudaMemsetAsync(d_daev.as<float>() + (size_t)row0 * ld_aev, 0, (size_t)R * ld_aev * sizeof(float), c->stream));
+    return f16::mlp_species_fused(c->stream, nets[s].hw, fwork, fo, M, nets[s].dims, (const __half*)d_aev_hi.p, (const __half*)d_aev_lo.p,
                                   ld_planes, nlocal, row0, R, d_daev.as<float>(), ld_aev, d_eatom.as<double>(), hm.sae[s], &c->launches);
+  }
   return f16::mlp_species(c->stream, nets[s].hw, hwork, M, nets[s].dims, (const __half*)d_aev_hi.p, (const __half*)d_aev_lo.p,
-                          ld_planes, nlocal, row0, R, d_daev.as<float>(), ld_aev, d_eatom.as<double>(), hm.sae[s], &c->launches);
+                          ld_planes, nlocal, row0, R, d_daev.as<float>(), ld_aev, d_eatom.as<double>(), hm.sae[s], &c->launches, c->opt_gemm_ctas);
 }
 
 template <> int Engine<double>::mlp_f16_all() {
@@ -846,67 +870,14 @@ template <> int Engine<double>::mlp_f16_all() {
   return 1;
 }
 
-// All species buckets through the launch-level software pipeline (mlp_f16_multi.cuh); ANI_B200_PIPE=0 or networks of
-// different depth fall back to one bucket after the other.
 template <> int Engine<float>::mlp_f16_all() {
-  static const int pipe = f16::env_int("ANI_B200_PIPE", 0);   // measured slower than bucket-by-bucket (profiles/README.md): off by default
-  int nh = -1;
-  bool same = true;
-  for (int s = 0; s < hm.S; s++) {
-    if (boff[s + 1] == boff[s]) continue;
-    if (!nets[s].hw.ready) { set_error("this network's layer widths are not supported by the f16 tensor-core path (need multiples of 32, <= 256)"); return 1; }
-    if (nh < 0) nh = nets[s].hw.nh; else same = same && (nh == nets[s].hw.nh);
-  }
-  if (nh < 0) return 0;
-  if (!pipe || !same || nh > f16::kMaxProb) {
-    for (int s = 0; s < hm.S; s++) {
-      const int R = boff[s + 1] - boff[s];
-      if (R == 0) continue;
-      if (int rc = mlp_f16_species(s, boff[s], R)) return rc;
-    }
-    return 0;
-  }
-  static const int chunk = (std::max(f16::env_int("ANI_B200_TC_CHUNK", 16384), 128) + 127) / 128 * 128;
-  std::vector<f16::Unit> units;
-  std::vector<int> maxw(nh + 1, 0);
-  int max_rows = 0;
   for (int s = 0; s < hm.S; s++) {
     const int R = boff[s + 1] - boff[s];
     if (R == 0) continue;
-    for (int l = 1; l <= nh; l++) maxw[l] = std::max(maxw[l], nets[s].dims[l]);
-    for (int r0 = 0; r0 < R; r0 += chunk) {
-      units.push_back(f16::Unit{s, boff[s] + r0, std::min(chunk, R - r0)});
-      max_rows = std::max(max_rows, units.back().R);
-    }
+    if (!nets[s].hw.ready) { set_error("this network's layer widths are not supported by the f16 tensor-core path (need multiples of 32, <= 256)"); return 1; }
+    if (int rc = mlp_f16_species(s, boff[s], R)) return rc;
   }
-  const int depth = 2 * nh - 1;
-  const size_t rows = (size_t)(max_rows + 127) / 128 * 128;
-  if ((int)hring.size() < depth) hring.resize(depth);
-  for (int k = 0; k < depth; k++) {
-    f16::Work& wk = hring[k];
-    if ((int)wk.H.size() < nh + 1) { wk.H.resize(nh + 1); wk.G.resize(nh + 1); }
-    for (int l = 1; l <= nh; l++) {
-      const size_t elems = rows * M * maxw[l];
-      if ((l < nh && !wk.H[l].reserve(elems)) || !wk.G[l].reserve(elems)) { set_error("out of memory for MLP work buffers"); return 1; }
-    }
-    if (!wk.e.reserve(rows * M * 4)) { set_error("out of memory for MLP work buffers"); return 1; }
-  }
-  static int num_sms = 0, max_smem = 0;
-  if (!num_sms) {
-    cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, c->device);
-    cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, c->device);
-  }
-  f16::PipeCtx pc{};
-  pc.st = c->stream; pc.M = M;
-  pc.aev_hi = (const __half*)d_aev_hi.p; pc.aev_lo = (const __half*)d_aev_lo.p; pc.ld_aev = ld_planes; pc.aev_rows_total = nlocal;
-  pc.daev = d_daev.as<float>(); pc.ld_daev = ld_aev; pc.eatom = d_eatom.as<double>(); pc.launches = &c->launches;
-  pc.num_sms = num_sms; pc.max_smem = max_smem;
-  pc.bk = f16::env_int("ANI_B200_BK", 32) == 64 ? 64 : 32;
-  pc.swz = f16::epi_swizzle();
-  std::vector<f16::SpeciesWeights*> W(hm.S);
-  std::vector<const std::vector<int>*> dm(hm.S);
-  for (int s = 0; s < hm.S; s++) { W[s] = &nets[s].hw; dm[s] = &nets[s].dims; }
-  return f16::mlp_pipeline(pc, units, W, dm, hm.sae, hring, nh);
+  return 0;
 }
 
 template <> int Engine<float>::mlp_tc_species(int s, int row0, int R) {
@@ -980,6 +951,11 @@ int ani_ctx_create(const ani_model* model, int device, int use_num_models, int u
     rc = e->init();
   }
   if (rc) return rc;
+  c->opt_mlp_fused = f16::env_int("ANI_B200_FUSED", 1) != 0;
+  c->opt_fused_prof = f16::env_int("ANI_B200_FUSED_PROF", 0) != 0;
+  c->opt_gemm_ctas = std::max(0, f16::env_int("ANI_B200_GEMM_CTAS", 0));
+  c->opt_aev_two_pass = f16::env_int("ANI_B200_AEV_TWO_PASS", 1) != 0;
+  c->opt_pin_user = f16::env_int("ANI_B200_PIN_USER", 0) != 0;
   const char* mode = getenv("ANI_B200_MLP_MODE");
   if (c->use_single) {
     // default: the tensor-core path that keeps fp32 parity, when every network's widths fit it; FFMA otherwise
@@ -1034,6 +1010,17 @@ int ani_ctx_synchronize(ani_ctx* c) {
   if (!c) { set_error("null context"); return 1; }
   ANIB_CUDA_OK(cudaSetDevice(c->device));
   ANIB_CUDA_OK(cudaStreamSynchronize(c->stream));
+  return c->eng ? c->eng->check_errors() : 0;
+}
+
+int ani_ctx_set_option(ani_ctx* c, const char* name, int value) {
+  if (!c || !name) { set_error("ani_ctx_set_option: null argument"); return 1; }
+  if (!strcmp(name, "mlp_fused")) c->opt_mlp_fused = value != 0;
+  else if (!strcmp(name, "fused_prof")) c->opt_fused_prof = value != 0;
+  else if (!strcmp(name, "gemm_ctas")) c->opt_gemm_ctas = value > 0 ? value : 0;
+  else if (!strcmp(name, "aev_two_pass")) c->opt_aev_two_pass = value != 0;
+  else if (!strcmp(name, "pin_user")) { c->opt_pin_user = value != 0; if (!value && c->eng) c->eng->release_pins(); }
+  else { set_error(std::string("ani_ctx_set_option: unknown option '") + name + "'"); return 1; }
   return 0;
 }
 

@@ -390,7 +390,9 @@ struct SpeciesWeights {
   HalfPlanes Wcat;                // [L][M*h1]                                 (scaled by sw[0])
   std::vector<float> sw;          // power-of-two scale of layer j's weight planes
   std::vector<DevBufTc> bias; // [j] : [M][dims[j+1]] fp32
+  std::vector<DevBufTc> bias_s;   // [j] : log2(e)/alpha * bias[j]   (the fused kernel's CELU epilogue works on the scaled value)
   DevBufTc w_out, b_out;      // [M][dims[nh]], [M]
+  DevBufTc w_out_s;           // kScaleG * w_out
 };
 
 struct Work {
@@ -426,11 +428,7 @@ inline int env_int(const char* name, int dflt) {
   return (e && *e) ? atoi(e) : dflt;
 }
 
-inline int epi_swizzle() {
-  static int v = -1;
-  if (v < 0) { const char* e = getenv("ANI_B200_EPI_SWIZZLE"); v = (e && atoi(e) == 0) ? 0 : 1; }
-  return v;
-}
+inline int epi_swizzle() { return 1; }   // swizzled staging buffers (bank-conflict-free 16-byte stores), matching tensor maps
 
 // scale w by the power of two that brings max|w| just below 2^14 and split into fp16 planes
 inline float pick_scale(const std::vector<float>& w) {
@@ -473,7 +471,7 @@ inline int prepare_species(const HostModel& hm, int M, int s, SpeciesWeights& w)
   if (!supported_dims(dims)) { w.ready = false; return 0; }
   const int nh = (int)dims.size() - 2;
   w.nh = nh;
-  w.Wf.resize(nh); w.WT.resize(nh); w.bias.resize(nh); w.sw.assign(nh, 1.f);
+  w.Wf.resize(nh); w.WT.resize(nh); w.bias.resize(nh); w.bias_s.resize(nh); w.sw.assign(nh, 1.f);
   for (int j = 0; j < nh; j++) {
     const int ni = dims[j], no = dims[j + 1];
     std::vector<float> f((size_t)M * no * ni), b((size_t)M * no);
@@ -484,6 +482,8 @@ inline int prepare_species(const HostModel& hm, int M, int s, SpeciesWeights& w)
     w.sw[j] = pick_scale(f);
     if (upload_half_planes(f, (size_t)ni, w.sw[j], w.Wf[j])) return 1;
     if (tc::upload_f32(b, w.bias[j])) return 1;
+    for (float& x : b) x *= 14.426950408889634f;   // kFScaleH (mlp_f16_fused.cuh)
+    if (tc::upload_f32(b, w.bias_s[j])) return 1;
     if (j >= 1) {
       std::vector<float> t((size_t)M * ni * no);
       for (int m = 0; m < M; m++)
@@ -508,6 +508,8 @@ inline int prepare_species(const HostModel& hm, int M, int s, SpeciesWeights& w)
       bo[m] = hm.b[m][s][nh][0];
     }
     if (tc::upload_f32(wo, w.w_out) || tc::upload_f32(bo, w.b_out)) return 1;
+    for (float& x : wo) x *= kScaleG;
+    if (tc::upload_f32(wo, w.w_out_s)) return 1;
   }
   w.ready = true;
   return 0;
@@ -528,9 +530,8 @@ inline int launch_gemm(const Launcher& L, const Operand& A, const Operand& B, co
                        uint64_t o_cols, uint64_t o_ld, const Operand& X, Args g) {
   CUtensorMap tA_hi, tA_lo, tB_hi, tB_lo, tO_hi, tO_lo, tX_hi, tX_lo;
   g.swz = epi_swizzle();
-  static const int cfg_bk = env_int("ANI_B200_BK", 32), cfg_epi = env_int("ANI_B200_EPI_WARPS", 8);
-  g.bk = (cfg_bk == 64) ? 64 : 32;
-  g.epi_warps = (cfg_epi == 4) ? 4 : 8;
+  g.bk = 32;          // measured best (profiles/README.md, round 1): 64-byte operand rows, twice the pipeline stages
+  g.epi_warps = 8;
   if (make_operand_map(&tA_hi, A.hi, A.rows, A.cols, A.ld, BM, g.bk) || make_operand_map(&tA_lo, A.lo, A.rows, A.cols, A.ld, BM, g.bk) ||
       make_operand_map(&tB_hi, B.hi, B.rows, B.cols, B.ld, (uint32_t)g.BN, g.bk) ||
       make_operand_map(&tB_lo, B.lo, B.rows, B.cols, B.ld, (uint32_t)g.BN, g.bk))
@@ -589,7 +590,7 @@ inline int64_t padded_rows(int nlocal) { return (int64_t)nlocal + BM; }
 // order; this bucket = rows [row0, row0+R).  daev: fp32 rows [.., ld_daev] in bucket order.
 inline int mlp_species(cudaStream_t st, SpeciesWeights& w, Work& work, int M, const std::vector<int>& dims, const __half* aev_hi,
                        const __half* aev_lo, int64_t ld_aev, int64_t aev_rows_total, int row0, int R, float* daev, int64_t ld_daev,
-                       double* eatom, double sae, int* launches) {
+                       double* eatom, double sae, int* launches, int cta_cap = 0) {
   if (!w.ready) { set_error("this network's layer widths are not supported by the f16 tensor-core path (need multiples of 32, <= 256)"); return 1; }
   static int num_sms = 0, max_smem = 0;
   if (!num_sms) {
@@ -598,9 +599,7 @@ inline int mlp_species(cudaStream_t st, SpeciesWeights& w, Work& work, int M, co
     cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev);
     cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
   }
-  static const int smem_cap_kb = env_int("ANI_B200_GEMM_SMEM_KB", 0);   // experiment: leave shared memory for co-resident kernels
-  static const int cta_cap = env_int("ANI_B200_GEMM_CTAS", 0);          // experiment: leave whole SMs to kernels on another stream
-  Launcher L{st, cta_cap > 0 ? std::min(num_sms, cta_cap) : num_sms, launches, smem_cap_kb > 0 ? std::min(max_smem, smem_cap_kb * 1024) : max_smem};
+  Launcher L{st, cta_cap > 0 ? std::min(num_sms, cta_cap) : num_sms, launches, max_smem};   // cta_cap: option "gemm_ctas" (leave SMs to another stream)
   const int nh = w.nh;
   int chunk = work.chunk_rows;
   if (chunk == 0) {

@@ -138,12 +138,13 @@ def ani2x_constants() -> Dict:
                 ShfZ=(np.arange(4) * 2 + 1) * math.pi / 8)
 
 
-def synthetic_ani2x(seed: int = 2024, num_models: int = 8) -> AniParams:
+def synthetic_ani2x(seed: int = 2024, num_models: int = 8, weight_scale: float = 1.0) -> AniParams:
     """ANI-2x geometry (1008-long AEV, 7 species, 8 members) with seeded random weights.
 
     Weights ~ N(0, 1/fan_in) and small biases: throughput does not depend on the values, and the
     CPU oracle evaluates the very same numbers, so parity tests are meaningful.  The output layer
-    is scaled so atomic energies are O(0.1 Ha) like the trained networks."""
+    is scaled so atomic energies are O(0.1 Ha) like the trained networks.  weight_scale multiplies the hidden-layer
+    weights (tests of the fp16 operand-range guard)."""
     c = ani2x_constants()
     rng = np.random.default_rng(seed)
     L = 7 * 16 + 28 * 32
@@ -158,6 +159,8 @@ def synthetic_ani2x(seed: int = 2024, num_models: int = 8) -> AniParams:
                 scale = (2.0 if l == 0 else 1.4) / math.sqrt(d[l])
                 if l == len(d) - 2:
                     scale = 0.3 / math.sqrt(d[l])
+                if l < len(d) - 2:
+                    scale *= weight_scale
                 W = (rng.standard_normal((d[l + 1], d[l])) * scale).astype(np.float32)
                 b = (rng.standard_normal(d[l + 1]) * 0.1).astype(np.float32)
                 per_l.append((W, b))

@@ -90,6 +90,9 @@ void PairANIB200::open_model() {
   if (ani_model_load(model_file.c_str(), &model)) fail("cannot load the model");
   if (ani_ctx_create(model, dev, use_num_models, use_cuaev ? 1 : 0, use_fullnbr ? 1 : 0, use_single ? 1 : 0, &ctx))
     fail("cannot create the CUDA context");
+  // atom->x and out_force keep their address between reallocations, and compute() releases the page-locks before either
+  // moves (nmax / vector growth): let the library DMA straight from / to them
+  ani_ctx_set_option(ctx, "pin_user", 1);
 }
 
 /* pair_style ani <cutoff> <model_file> <cpu|cuda> [num_models] [cuaev|pyaev] [full|half] [single|double] */

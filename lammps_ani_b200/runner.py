@@ -43,6 +43,7 @@ def load_library():
     L.ani_ctx_create.argtypes = [vp, i32, i32, i32, i32, i32, C.POINTER(vp)]
     L.ani_ctx_destroy.argtypes = [vp]
     L.ani_ctx_set_mlp_mode.argtypes = [vp, i32]
+    L.ani_ctx_set_option.argtypes = [vp, C.c_char_p, i32]
     L.ani_ctx_set_stream.argtypes = [vp, vp]
     L.ani_ctx_synchronize.argtypes = [vp]
     L.ani_ctx_reset_stream.argtypes = [vp]
@@ -63,7 +64,7 @@ def load_library():
     L.ani_debug_tc_gemm.restype = i32
     L.ani_halo_pack_x.argtypes = [vp, vp, i32, vp, vp, i64, vp]
     L.ani_halo_unpack_add_f.argtypes = [vp, vp, i32, vp, vp, i64]
-    for name in ("ani_model_load", "ani_model_info", "ani_ctx_create", "ani_ctx_set_mlp_mode", "ani_ctx_set_stream",
+    for name in ("ani_model_load", "ani_model_info", "ani_ctx_create", "ani_ctx_set_mlp_mode", "ani_ctx_set_option", "ani_ctx_set_stream",
                  "ani_ctx_reset_stream", "ani_ctx_synchronize", "ani_ctx_enable_timing", "ani_last_timing", "ani_set_neighbors_full",
                  "ani_set_neighbors_half", "ani_set_neighbors_table", "ani_device_count", "ani_compute",
                  "ani_compute_device", "ani_debug_get_aev", "ani_halo_pack_x", "ani_halo_unpack_add_f", "ani_build_neighbors",
@@ -78,7 +79,7 @@ EXPORTED_SYMBOLS = [
     "ani_ctx_set_stream", "ani_ctx_reset_stream", "ani_ctx_synchronize", "ani_set_neighbors_full", "ani_set_neighbors_half", "ani_compute",
     "ani_compute_device", "ani_halo_pack_x", "ani_halo_unpack_add_f", "ani_debug_get_aev", "ani_last_timing",
     "ani_ctx_enable_timing", "ani_last_error", "ani_abi_version", "ani_debug_tc_gemm", "ani_set_neighbors_table",
-    "ani_device_count", "ani_build_neighbors", "ani_debug_get_neighbors", "ani_ctx_release_host_buffers",
+    "ani_device_count", "ani_build_neighbors", "ani_debug_get_neighbors", "ani_ctx_release_host_buffers", "ani_ctx_set_option",
 ]
 
 
@@ -142,6 +143,13 @@ class ANI:
     # ---- knobs
     def set_mlp_mode(self, mode: int):
         _check(self._L.ani_ctx_set_mlp_mode(self._ctx, mode))
+
+    def set_option(self, name: str, value: int):
+        """Per-context switch (include/ani_b200.h: "mlp_fused", "pin_user", "aev_two_pass", "gemm_ctas", "fused_prof")."""
+        _check(self._L.ani_ctx_set_option(self._ctx, name.encode(), int(value)))
+
+    def release_host_buffers(self):
+        _check(self._L.ani_ctx_release_host_buffers(self._ctx))
 
     def set_stream(self, cuda_stream_ptr: Optional[int]):
         """Run on this cudaStream_t (0 = the legacy default stream); None = back to the context's own stream."""

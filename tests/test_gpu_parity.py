@@ -205,6 +205,7 @@ def test_stable_caller_buffers_are_pinned_in_place(ANI, ani2x_synth_path):
     x, sp, box = domain.make_water_box((6, 6, 5), seed=9)
     sub, il, nn, jl = periodic_system(x, sp, box)
     ani = ANI(ani2x_synth_path, 0, -1, True, True, True)
+    ani.set_option("pin_user", 1)      # opt-in: the caller promises release_host_buffers() before the arrays go away
     e0, f0, _, _ = ani.compute(sub.species, sub.x.copy(), il, jl, nn, nlocal=sub.nlocal, ago=0)
     xs = np.ascontiguousarray(sub.x, dtype=np.float64)
     fs = np.full((sub.x.shape[0], 3), np.nan)

@@ -90,8 +90,10 @@ def test_f16x3_gemm_matches_fp64(runner, R, N, K):
     assert err.max() < 1e-4
 
 
+@pytest.mark.parametrize("fused", [1, 0])
 @pytest.mark.parametrize("model", ["ani2x_synth", "ani1xnr"])
-def test_full_path_f16x3_parity(runner, ani2x_synth_path, ani1xnr_path, model):
+def test_full_path_f16x3_parity(runner, ani2x_synth_path, ani1xnr_path, model, fused):
+    """fused 1: the whole network of a bucket in one kernel (mlp_f16_fused.cuh, the default); 0: layer by layer (mlp_f16.cuh)."""
     path = ani2x_synth_path if model == "ani2x_synth" else ani1xnr_path
     x, sp, box = domain.make_water_box((8, 9, 10), seed=7)
     sub = domain.decompose(x, sp, box)[0]
@@ -99,12 +101,90 @@ def test_full_path_f16x3_parity(runner, ani2x_synth_path, ani1xnr_path, model):
     ref = OracleANI(path).compute_full(sub.species, sub.x, il, nn, jl, sub.nlocal, single_coords=True, want_aev=True, want_daev=True)
     ani = runner.ANI(path, 0, -1, True, True, True)
     ani.set_mlp_mode(runner.MLP_F16X3)
+    ani.set_option("mlp_fused", fused)
     e, f, eatom, virial = ani.compute(sub.species, sub.x, il, jl, nn, nlocal=sub.nlocal, ago=0, atomic=True, vflag=True)
     aev, daev = ani.debug_aev()
-    print("f16x3: aev max err", np.abs(aev - ref["aev"]).max(), "daev max err", np.abs(daev - ref["daev"]).max(),
+    print(f"f16x3 fused={fused}: aev max err", np.abs(aev - ref["aev"]).max(), "daev max err", np.abs(daev - ref["daev"]).max(),
           "force max err", np.abs(f - ref["forces"]).max(), "E rel err", abs(e - ref["energy"]) / abs(ref["energy"]))
     assert np.abs(aev - ref["aev"]).max() <= 2e-5 * max(1.0, np.abs(ref["aev"]).max())
     assert abs(e - ref["energy"]) <= 1e-6 * abs(ref["energy"])
     assert np.abs(f - ref["forces"]).max() <= 1e-4 * EV2KCAL
     assert np.abs(eatom - ref["eatom"]).max() <= 1e-5 * np.abs(ref["eatom"]).max()
     assert np.abs(virial - ref["virial"]).max() <= 1e-4 * max(1.0, np.abs(ref["virial"]).max())
+
+
+def _mixed_box(cells, seed, species_pool, nswap):
+    rng = np.random.default_rng(seed)
+    x, sp, box = domain.make_water_box(cells, seed=seed)
+    sp = sp.copy()
+    pick = rng.choice(len(sp), size=nswap, replace=False)
+    sp[pick] = rng.choice(species_pool, size=nswap)
+    sub = domain.decompose(x, sp, box)[0]
+    il, nn, jl = domain.full_neighbor_list(sub.x, sub.nlocal)
+    return sub, il, nn, jl
+
+
+@pytest.mark.parametrize("fused", [1, 0])
+def test_f16x3_mixed_species_wide_aev(runner, ani2x_synth_path, fused):
+    """H, C, N, O present: 384 active AEV columns (> 256), so the fused kernel hands g1 to a separate dE/dAEV GEMM; tiny
+    C / N buckets (a single ragged row tile)."""
+    sub, il, nn, jl = _mixed_box((6, 6, 5), 21, [1, 2], 40)
+    ref = OracleANI(ani2x_synth_path).compute_full(sub.species, sub.x, il, nn, jl, sub.nlocal, single_coords=True, want_daev=True)
+    ani = runner.ANI(ani2x_synth_path, 0, -1, True, True, True)
+    ani.set_option("mlp_fused", fused)
+    e, f, eatom, virial = ani.compute(sub.species, sub.x, il, jl, nn, nlocal=sub.nlocal, ago=0, atomic=True, vflag=True)
+    _, daev = ani.debug_aev()
+    print(f"mixed fused={fused}: daev max err", np.abs(daev - ref["daev"]).max(), "force max err", np.abs(f - ref["forces"]).max(),
+          "E rel err", abs(e - ref["energy"]) / abs(ref["energy"]))
+    assert abs(e - ref["energy"]) <= 1e-6 * abs(ref["energy"])
+    assert np.abs(f - ref["forces"]).max() <= 1e-4 * EV2KCAL
+    assert np.abs(eatom - ref["eatom"]).max() <= 1e-5 * np.abs(ref["eatom"]).max()
+    assert np.abs(virial - ref["virial"]).max() <= 1e-4 * max(1.0, np.abs(ref["virial"]).max())
+
+
+def test_fused_matches_layerwise_many_items_per_cta(runner, ani2x_synth_path):
+    """12 288 atoms: 512 + 256 work items over 148 CTAs, so every CTA pipelines several items back to back (ring phases wrap,
+    TMEM regions are reused across items); repeated steps must reproduce, and the fused kernel must agree with the
+    layer-by-layer kernels to fp32 noise."""
+    x, sp, box = domain.make_water_box((16, 16, 16), seed=4)
+    sub = domain.decompose(x, sp, box)[0]
+    il, nn, jl = domain.full_neighbor_list(sub.x, sub.nlocal)
+    out = {}
+    for fused in (0, 1):
+        ani = runner.ANI(ani2x_synth_path, 0, -1, True, True, True)
+        ani.set_option("mlp_fused", fused)
+        e, f, eatom, _ = ani.compute(sub.species, sub.x, il, jl, nn, nlocal=sub.nlocal, ago=0, atomic=True)
+        for _ in range(3):
+            e2, f2, eatom2, _ = ani.compute(sub.species, sub.x, nlocal=sub.nlocal, ago=1, atomic=True)
+            assert abs(e2 - e) <= 1e-9 * abs(e) and np.abs(f2 - f).max() <= 1e-3   # fp32 atomics: summation order only
+        out[fused] = (e, f, eatom)
+    (e0, f0, a0), (e1, f1, a1) = out[0], out[1]
+    print("fused vs layerwise: E rel", abs(e1 - e0) / abs(e0), "F max", np.abs(f1 - f0).max(), "eatom max", np.abs(a1 - a0).max())
+    assert abs(e1 - e0) <= 2e-7 * abs(e0)
+    assert np.abs(f1 - f0).max() <= 0.5e-4 * EV2KCAL
+    assert np.abs(a1 - a0).max() <= 2e-6 * np.abs(a0).max()
+
+
+@pytest.mark.parametrize("fused", [1])
+def test_f16_operand_range_guard(runner, tmp_path, fused):
+    """Weights x64 on a compressed box: activations leave the fp16 range of the f16x3 planes (|16 h| >= 65504).  The library
+    must say so (status 3 -> RuntimeError) instead of returning inf / nan forces; a tf32x3 context evaluates the same
+    system."""
+    from lammps_ani_b200 import aniw, extract
+    p = str(tmp_path / "big.aniw")
+    big = extract.synthetic_ani2x(seed=7, weight_scale=64.0)
+    aniw.save(big, p)
+    x, sp, box = domain.make_water_box((5, 5, 5), seed=3)
+    x = x * 0.6
+    box = np.asarray(box) * 0.6
+    sub = domain.decompose(x, sp, box)[0]
+    il, nn, jl = domain.full_neighbor_list(sub.x, sub.nlocal)
+    ani = runner.ANI(p, 0, -1, True, True, True)
+    ani.set_option("mlp_fused", fused)
+    with pytest.raises(RuntimeError, match="fp16 operand range"):
+        ani.compute(sub.species, sub.x, il, jl, nn, nlocal=sub.nlocal, ago=0)
+    # the flag is cleared once reported, and the strict fp32 path handles the same system
+    ani2 = runner.ANI(p, 0, -1, True, True, True)
+    ani2.set_mlp_mode(runner.MLP_FP32_SIMT)
+    e, f, _, _ = ani2.compute(sub.species, sub.x, il, jl, nn, nlocal=sub.nlocal, ago=0)
+    assert np.isfinite(e) and np.isfinite(f).all()
