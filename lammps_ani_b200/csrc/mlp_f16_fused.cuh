@@ -87,6 +87,24 @@ __device__ __forceinline__ bool elect_one() {
   return pred != 0;
 }
 
+// 8 consecutive accumulator columns of this thread's TMEM lane.  The _nowait form only issues the load; tmem_ld_wait8 waits
+// for it and hands the values over (the "+r" operands keep the compiler from reading them earlier).
+__device__ __forceinline__ void tmem_ld8_nowait(uint32_t taddr, uint32_t (&v)[8]) {
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]) : "r"(taddr));
+}
+__device__ __forceinline__ void tmem_ld_wait8(uint32_t (&vn)[8], uint32_t (&v)[8]) {
+  asm volatile("tcgen05.wait::ld.sync.aligned;" : "+r"(vn[0]), "+r"(vn[1]), "+r"(vn[2]), "+r"(vn[3]), "+r"(vn[4]), "+r"(vn[5]), "+r"(vn[6]),
+               "+r"(vn[7]) :: "memory");
+#pragma unroll
+  for (int i = 0; i < 8; i++) v[i] = vn[i];
+}
+__device__ __forceinline__ void tmem_ld8(uint32_t taddr, uint32_t (&v)[8]) {
+  tmem_ld8_nowait(taddr, v);
+  asm volatile("tcgen05.wait::ld.sync.aligned;" : "+r"(v[0]), "+r"(v[1]), "+r"(v[2]), "+r"(v[3]), "+r"(v[4]), "+r"(v[5]), "+r"(v[6]), "+r"(v[7])
+               :: "memory");
+}
+
 // plain (non-tensor) bulk copy global -> shared, completion on an mbarrier
 __device__ __forceinline__ void bulk_load(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
   asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst), "l"(src), "r"(bytes),
@@ -174,7 +192,7 @@ f16_fused_kernel(const __grid_constant__ FusedMaps maps, const __grid_constant__
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < kFNB; i++) { mbar_init(bfull(i), 1); mbar_init(bempty(i), 1); }
     for (int i = 0; i < kFNA; i++) { mbar_init(afull(i), 1); mbar_init(aempty(i), 1); }
-    for (int i = 0; i < kFG; i++) { mbar_init(hfull(i), 4); mbar_init(hfree(i), 1); mbar_init(dfull(i), 4); }
+    for (int i = 0; i < kFG; i++) { mbar_init(hfull(i), 4 * kFG); mbar_init(hfree(i), 1); mbar_init(dfull(i), 4 * kFG); }
     for (int i = 0; i < 2; i++) { mbar_init(accfull(i), 1); mbar_init(accfree(i), 4 * kFG); mbar_init(cfull(i), 1); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -347,20 +365,23 @@ f16_fused_kernel(const __grid_constant__ FusedMaps maps, const __grid_constant__
     }
   } else if (warp >= 4) {
     // ================================================================= epilogue warps
-    // group of the HIGHEST warp ids takes block 0: the warp scheduler favours high warp ids, which staggers the groups' blocks
-    // (block 0 first) instead of finishing all four at once -- the MMAs of the next stage start earlier
-    const int q = warp & 3, grp = (kFG - 1) - ((warp - 4) >> 2);
+    // Every 128 x 32 output block is produced by ALL sixteen warps: warp (quadrant q, slice j) converts columns 8j..8j+7 of
+    // rows 32q..32q+31, one 16-byte chunk per plane.  Blocks therefore complete one after the other, a quarter of a "round"
+    // apart, and the next stage's MMAs follow one block behind (with one warp group per block, four blocks used to land at
+    // the same moment: the tensor pipe idled for a whole round at every stage boundary).  TMEM slices and CELU' vectors are
+    // fetched one block ahead.
+    const int q = warp & 3, j8 = (warp - 4) >> 2;                 // lane quadrant, 8-column slice inside a block
     const int r = q * 32 + lane;                                  // row inside the 128-row tile
-    const uint32_t blk = baseH + (uint32_t)grp * kFBlk;           // this group's output-block slot
     float4* const scr = (float4*)(g.scratch + (size_t)blockIdx.x * g.scratch_per_cta);
     const int n1 = g.N[0];
-    uint32_t huse = 0, t = 0, cuse[2] = {0, 0};
+    uint32_t hpar = 0, t = 0, cuse[2] = {0, 0};                   // hpar bit i: parity of the uses of output-block slot i so far
     long long w_acc = 0, w_h = 0, t_begin = 0;
     const bool prof_me = PROF && warp == 4 && lane == 0;
     if (prof_me) t_begin = clock64();
-    // float4 index of (block cb, quadrant q, vector 0, lane) in a CELU' scratch area; vector j is 32 float4 further on, so a
-    // warp's store / load of one vector is 512 contiguous bytes
-    auto dvec0 = [&](int cb) { return ((cb * 4 + q) * 8) * 32 + lane; };
+    // float4 index of (block cb, quadrant q, vector 2*j8, lane) in a CELU' scratch area; a warp's store / load of one vector is
+    // 512 contiguous bytes
+    auto dvec0 = [&](int cb) { return ((cb * 4 + q) * 8 + 2 * j8) * 32 + lane; };
+    const uint32_t lane_taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(8 * j8);
 
     for (int it = blockIdx.x; it < num_items; it += gridDim.x) {
       const int rt = it / g.batch, z = it % g.batch;
@@ -380,17 +401,17 @@ f16_fused_kernel(const __grid_constant__ FusedMaps maps, const __grid_constant__
         cuse[rr]++;
         return baseC + rr * (uint32_t)g.cslot_bytes;
       };
-      auto wait_slot = [&]() {
+      auto wait_slot = [&](int slot) {           // the previous block in this slot has been consumed
         long long c0 = 0;
         if (prof_me) c0 = clock64();
-        mbar_wait_wd(hfree(grp), (huse & 1u) ^ 1u, g.dbg, WD(5, grp));
+        mbar_wait_wd(hfree(slot), ((hpar >> slot) & 1u) ^ 1u, g.dbg, WD(5, slot));
+        hpar ^= 1u << slot;
         if (prof_me) w_h += clock64() - c0;
       };
-      auto publish = [&](bool last_stage) {
+      auto publish = [&](int slot, bool last_stage) {
         fence_async_smem();
         __syncwarp();
-        if (lane == 0) mbar_arrive(last_stage ? dfull(grp) : hfull(grp));
-        huse++;
+        if (lane == 0) mbar_arrive(last_stage ? dfull(slot) : hfull(slot));
       };
       auto end_stage = [&]() {
         tc_fence_before();
@@ -398,7 +419,19 @@ f16_fused_kernel(const __grid_constant__ FusedMaps maps, const __grid_constant__
         if (lane == 0) mbar_arrive(accfree(t & 1u));
         t++;
       };
-      auto taddr = [&](int cb) { return tmem_base + ((uint32_t)(q * 32) << 16) + (t & 1u) * 256u + (uint32_t)(cb * 32); };
+      auto tslice = [&](int cb) { return lane_taddr + (t & 1u) * 256u + (uint32_t)(cb * 32); };
+      // hi / lo planes of 8 values -> chunk j8 of row r in block slot `slot`
+      auto put8 = [&](int slot, const float (&x)[8]) {
+        uint32_t hh[4], ll[4];
+#pragma unroll
+        for (int e = 0; e < 4; e++) {
+          amax = fmaxf(fmaxf(fabsf(x[2 * e]), fabsf(x[2 * e + 1])), amax);
+          split2(x[2 * e], x[2 * e + 1], hh[e], ll[e]);
+        }
+        const uint32_t dst = baseH + (uint32_t)slot * kFBlk + blk_off64(r, j8);
+        sts128(dst, hh[0], hh[1], hh[2], hh[3]);
+        sts128(dst + kFBlk / 2, ll[0], ll[1], ll[2], ll[3]);
+      };
 
       // ---------------- S0, S1: u = kFScaleH * z = acc*a + b';  h = CELU -> planes (x kFScaleH);  CELU'(z) -> scratch
 #pragma unroll 1
@@ -407,30 +440,29 @@ f16_fused_kernel(const __grid_constant__ FusedMaps maps, const __grid_constant__
         const float a = kFScaleH * g.acc_scale[s];
         float4* const dst = scr + (s == 0 ? 0 : n1 * 32);       // n1*128 floats = n1*32 float4
         wait_acc();
-        const uint32_t cb_s = wait_consts();
+        const uint32_t cb_s = wait_consts() + (uint32_t)j8 * 32u;
+        uint32_t v[8], vn[8];
+        tmem_ld8(tslice(0), v);
 #pragma unroll 1
-        for (int cb = grp; cb < nb; cb += kFG) {
-          uint32_t v[32];
-          tmem_ld32(taddr(cb), v);
-          float4* const dp = dst + dvec0(cb);
-          const uint32_t bsm = cb_s + (uint32_t)cb * 128u;
-          wait_slot();
+        for (int cb = 0; cb < nb; cb++) {
+          const int slot = cb & (kFG - 1);
+          if (cb + 1 < nb) tmem_ld8_nowait(tslice(cb + 1), vn);
+          const float4 b0 = lds_f4(cb_s + (uint32_t)cb * 128u), b1 = lds_f4(cb_s + (uint32_t)cb * 128u + 16u);
+          const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+          float h[8], d[8];
 #pragma unroll
-          for (int ch = 0; ch < 4; ch++) {
-            const float4 b0 = lds_f4(bsm + ch * 32), b1 = lds_f4(bsm + ch * 32 + 16);
-            const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
-            float h[8], d[8];
-#pragma unroll
-            for (int e = 0; e < 8; e++) {
-              const float u = fmaf(__uint_as_float(v[ch * 8 + e]), a, bb[e]);   // log2(e)/alpha * z
-              d[e] = fminf(exp2f(u), 1.f);                                      // CELU'(z) = min(e^(z/alpha), 1)
-              h[e] = fmaxf(u, fmaf(kFCeluC, d[e], -kFCeluC));                   // kFScaleH * CELU(z)   (e^x - 1 >= x)
-            }
-            __stcg(dp + (2 * ch) * 32, make_float4(d[0], d[1], d[2], d[3]));
-            __stcg(dp + (2 * ch + 1) * 32, make_float4(d[4], d[5], d[6], d[7]));
-            put_planes8(blk, r, ch, h, amax);
+          for (int e = 0; e < 8; e++) {
+            const float u = fmaf(__uint_as_float(v[e]), a, bb[e]);            // log2(e)/alpha * z
+            d[e] = fminf(exp2f(u), 1.f);                                      // CELU'(z) = min(e^(z/alpha), 1)
+            h[e] = fmaxf(u, fmaf(kFCeluC, d[e], -kFCeluC));                   // kFScaleH * CELU(z)   (e^x - 1 >= x)
           }
-          publish(false);
+          float4* const dp = dst + dvec0(cb);
+          __stcg(dp, make_float4(d[0], d[1], d[2], d[3]));
+          __stcg(dp + 32, make_float4(d[4], d[5], d[6], d[7]));
+          wait_slot(slot);
+          put8(slot, h);
+          publish(slot, false);
+          if (cb + 1 < nb) tmem_ld_wait8(vn, v);
         }
         end_stage();
       }
@@ -439,36 +471,35 @@ f16_fused_kernel(const __grid_constant__ FusedMaps maps, const __grid_constant__
         const int nb = g.N[2] >> 5;
         const float a = kFScaleH * g.acc_scale[2];
         wait_acc();
-        const uint32_t cb_s = wait_consts();
-        const uint32_t wsm0 = cb_s + (uint32_t)g.N[2] * 4u;
+        const uint32_t cb_s = wait_consts() + (uint32_t)j8 * 32u;
+        const uint32_t w_s = cb_s + (uint32_t)g.N[2] * 4u;
+        uint32_t v[8], vn[8];
+        tmem_ld8(tslice(0), v);
 #pragma unroll 1
-        for (int cb = grp; cb < nb; cb += kFG) {
-          uint32_t v[32];
-          tmem_ld32(taddr(cb), v);
-          const uint32_t bsm = cb_s + (uint32_t)cb * 128u, wsm = wsm0 + (uint32_t)cb * 128u;
-          wait_slot();
+        for (int cb = 0; cb < nb; cb++) {
+          const int slot = cb & (kFG - 1);
+          if (cb + 1 < nb) tmem_ld8_nowait(tslice(cb + 1), vn);
+          const float4 b0 = lds_f4(cb_s + (uint32_t)cb * 128u), b1 = lds_f4(cb_s + (uint32_t)cb * 128u + 16u);
+          const float4 w0 = lds_f4(w_s + (uint32_t)cb * 128u), w1 = lds_f4(w_s + (uint32_t)cb * 128u + 16u);
+          const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+          const float ww[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
+          float gg[8];
 #pragma unroll
-          for (int ch = 0; ch < 4; ch++) {
-            const float4 b0 = lds_f4(bsm + ch * 32), b1 = lds_f4(bsm + ch * 32 + 16);
-            const float4 w0 = lds_f4(wsm + ch * 32), w1 = lds_f4(wsm + ch * 32 + 16);
-            const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
-            const float ww[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
-            float gg[8];
-#pragma unroll
-            for (int e = 0; e < 8; e++) {
-              const float u = fmaf(__uint_as_float(v[ch * 8 + e]), a, bb[e]);
-              const float d = fminf(exp2f(u), 1.f);
-              const float h = fmaxf(u, fmaf(kFCeluC, d, -kFCeluC));
-              e_acc = fmaf(h, ww[e], e_acc);                    // x kFScaleH * kScaleG, folded back below
-              gg[e] = ww[e] * d;
-            }
-            put_planes8(blk, r, ch, gg, amax);
+          for (int e = 0; e < 8; e++) {
+            const float u = fmaf(__uint_as_float(v[e]), a, bb[e]);
+            const float d = fminf(exp2f(u), 1.f);
+            const float h = fmaxf(u, fmaf(kFCeluC, d, -kFCeluC));
+            e_acc = fmaf(h, ww[e], e_acc);                      // x kFScaleH * kScaleG, folded back below
+            gg[e] = ww[e] * d;
           }
-          publish(false);
+          wait_slot(slot);
+          put8(slot, gg);
+          publish(slot, false);
+          if (cb + 1 < nb) tmem_ld_wait8(vn, v);
         }
         end_stage();
-        if (row < g.R)                                          // e_out is zeroed before the launch; the groups add their parts
-          atomicAdd(g.e_out + (size_t)row * g.e_ld + z, e_acc * (1.0f / (kFScaleH * kScaleG)) + (grp == 0 ? __ldg(g.b_out + z) : 0.f));
+        if (row < g.R)                                          // e_out is zeroed before the launch; the column slices add their parts
+          atomicAdd(g.e_out + (size_t)row * g.e_ld + z, e_acc * (1.0f / (kFScaleH * kScaleG)) + (j8 == 0 ? __ldg(g.b_out + z) : 0.f));
       }
       // ---------------- S3, S4: g = acc * s * CELU'(z) (from scratch) -> planes
 #pragma unroll 1
@@ -476,33 +507,27 @@ f16_fused_kernel(const __grid_constant__ FusedMaps maps, const __grid_constant__
         const int nb = g.N[s] >> 5;
         const float a = g.acc_scale[s];
         const float4* const src = scr + (s == 3 ? n1 * 32 : 0);
-        float4 dd[8];
-        if (grp < nb) {                                         // the first block's CELU' does not need the accumulator
-          const float4* const dp = src + dvec0(grp);
-#pragma unroll
-          for (int j = 0; j < 8; j++) dd[j] = __ldcg(dp + j * 32);
-        }
+        float4 d0 = __ldcg(src + dvec0(0)), d1 = __ldcg(src + dvec0(0) + 32);   // the first block's CELU' does not need the accumulator
         wait_acc();
+        uint32_t v[8], vn[8];
+        tmem_ld8(tslice(0), v);
 #pragma unroll 1
-        for (int cb = grp; cb < nb; cb += kFG) {
-          if (cb != grp) {
-            const float4* const dp = src + dvec0(cb);
-#pragma unroll
-            for (int j = 0; j < 8; j++) dd[j] = __ldcg(dp + j * 32);
+        for (int cb = 0; cb < nb; cb++) {
+          const int slot = cb & (kFG - 1);
+          float4 d0n = d0, d1n = d1;
+          if (cb + 1 < nb) {
+            tmem_ld8_nowait(tslice(cb + 1), vn);
+            d0n = __ldcg(src + dvec0(cb + 1)); d1n = __ldcg(src + dvec0(cb + 1) + 32);
           }
-          uint32_t v[32];
-          tmem_ld32(taddr(cb), v);
-          wait_slot();
+          const float d8[8] = {d0.x, d0.y, d0.z, d0.w, d1.x, d1.y, d1.z, d1.w};
+          float gg[8];
 #pragma unroll
-          for (int ch = 0; ch < 4; ch++) {
-            const float d8[8] = {dd[2 * ch].x, dd[2 * ch].y, dd[2 * ch].z, dd[2 * ch].w,
-                                 dd[2 * ch + 1].x, dd[2 * ch + 1].y, dd[2 * ch + 1].z, dd[2 * ch + 1].w};
-            float gg[8];
-#pragma unroll
-            for (int e = 0; e < 8; e++) gg[e] = __uint_as_float(v[ch * 8 + e]) * a * d8[e];
-            put_planes8(blk, r, ch, gg, amax);
-          }
-          publish(s == ns - 1);
+          for (int e = 0; e < 8; e++) gg[e] = __uint_as_float(v[e]) * a * d8[e];
+          wait_slot(slot);
+          put8(slot, gg);
+          publish(slot, s == ns - 1);
+          if (cb + 1 < nb) tmem_ld_wait8(vn, v);
+          d0 = d0n; d1 = d1n;
         }
         end_stage();
       }
@@ -512,15 +537,17 @@ f16_fused_kernel(const __grid_constant__ FusedMaps maps, const __grid_constant__
         const float a = g.acc_scale[5];
         wait_acc();
 #pragma unroll 1
-        for (int cb = grp; cb < nb; cb += kFG) {
-          uint32_t v[32];
-          tmem_ld32(taddr(cb), v);
-          wait_slot();
-#pragma unroll
-          for (int c4 = 0; c4 < 8; c4++)
-            sts128(blk + blk_off128(r, c4), __float_as_uint(__uint_as_float(v[4 * c4]) * a), __float_as_uint(__uint_as_float(v[4 * c4 + 1]) * a),
-                   __float_as_uint(__uint_as_float(v[4 * c4 + 2]) * a), __float_as_uint(__uint_as_float(v[4 * c4 + 3]) * a));
-          publish(true);
+        for (int cb = 0; cb < nb; cb++) {
+          const int slot = cb & (kFG - 1);
+          uint32_t v[8];
+          tmem_ld8(tslice(cb), v);
+          wait_slot(slot);
+          const uint32_t dst = baseH + (uint32_t)slot * kFBlk;
+          sts128(dst + blk_off128(r, 2 * j8), __float_as_uint(__uint_as_float(v[0]) * a), __float_as_uint(__uint_as_float(v[1]) * a),
+                 __float_as_uint(__uint_as_float(v[2]) * a), __float_as_uint(__uint_as_float(v[3]) * a));
+          sts128(dst + blk_off128(r, 2 * j8 + 1), __float_as_uint(__uint_as_float(v[4]) * a), __float_as_uint(__uint_as_float(v[5]) * a),
+                 __float_as_uint(__uint_as_float(v[6]) * a), __float_as_uint(__uint_as_float(v[7]) * a));
+          publish(slot, true);
         }
         end_stage();
       }
