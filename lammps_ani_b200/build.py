@@ -52,5 +52,19 @@ def build_plugin(force: bool = False) -> str:
     return PLUGIN
 
 
+TEST_MODEL = os.path.join(HERE, "..", "tools", "test_model")
+
+
+def build_test_model(force: bool = False) -> str:
+    """The stand-alone C++ known-answer driver (tools/test_model.cpp; reference: src/ani_csrc/test_model.cpp)."""
+    src = os.path.join(HERE, "..", "tools", "test_model.cpp")
+    deps = [src, os.path.join(HERE, "..", "tools", "test_model_golden.h"), LIB]
+    if not force and os.path.exists(TEST_MODEL) and all(os.path.getmtime(d) < os.path.getmtime(TEST_MODEL) for d in deps):
+        return TEST_MODEL
+    subprocess.check_call(["/usr/bin/g++", "-O2", "-std=c++17", src, "-o", TEST_MODEL, f"-L{HERE}", "-lani_b200",
+                           f"-Wl,-rpath,{HERE}"])
+    return TEST_MODEL
+
+
 if __name__ == "__main__":
     print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))

@@ -154,7 +154,11 @@ void PairANIB200::init_style() {
   // the same full list (all j within cutoff + skin of a local i, ghosts included) on the GPU from atom->x
   // (ani_build_neighbors).  LAMMPS still decides WHEN to rebuild (neigh_modify, displacement check) and still sizes the ghost
   // shell from cutoff + skin; its own CPU binning / list build and the host flatten + H2D of the list disappear.
-  if (device_list) return;
+  if (device_list) {
+    // the device build bins in Cartesian space over [sublo - cutghost, subhi + cutghost): orthogonal boxes only
+    if (domain->triclinic) error->all(FLERR, "Pair style ANI: ani_neighbor device needs an orthogonal box (use full or half)");
+    return;
+  }
   if (use_fullnbr) neighbor->add_request(this, NeighConst::REQ_FULL);
   else neighbor->add_request(this);
 }

@@ -191,7 +191,7 @@ def read_torchscript_params(pt_path: str):
     # ---- networks.  Form (b): stacked BmmEnsemble weights [M, in, out] / [M, out, in] per species
     nn_keys = [k for k in flat if k.endswith(".weight") and isinstance(flat[k], np.ndarray) and "neural_networks" in k]
     if not nn_keys:
-        nn_keys = [k for k in flat if k.endswith(".weight") and isinstance(flat[k], np.ndarray)]
+        nn_keys = [k for k in flat if k.endswith(".weight") and isinstance(flat[k], np.ndarray) and not k.startswith("rep_calc.")]
     if not nn_keys:
         raise ValueError(f"{pt_path}: no Linear weights found")
     stacked = all(flat[k].ndim == 3 for k in nn_keys)
@@ -202,7 +202,23 @@ def read_torchscript_params(pt_path: str):
         for k in nn_keys:
             parts = k.split(".")
             groups.setdefault(".".join(parts[:-2]), []).append(k)
-        gkeys = sorted(groups, key=lambda k: [int(t) if t.isdigit() else t for t in k.split(".")])
+        # species order = the model's: an integer path component indexes `symbols`, a symbol component is looked up in it
+        # (a ModuleDict keyed by element symbol must NOT be sorted alphabetically); otherwise keep the archive's own order
+        def species_of(gk):
+            for t in reversed(gk.split(".")):
+                if t in symbols:
+                    return symbols.index(t)
+            return None
+        by_symbol = {gk: species_of(gk) for gk in groups}
+        if all(v is not None for v in by_symbol.values()) and len(set(by_symbol.values())) == len(groups):
+            gkeys = sorted(groups, key=lambda gk: by_symbol[gk])
+        else:
+            def int_key(gk):
+                ints = [int(t) for t in gk.split(".") if t.isdigit()]
+                if not ints:
+                    raise ValueError(f"{pt_path}: cannot tell which species the network group '{gk}' belongs to")
+                return ints
+            gkeys = sorted(groups, key=int_key)
         if len(gkeys) != S:
             raise ValueError(f"{pt_path}: expected {S} per-species network groups, found {len(gkeys)}: {gkeys}")
         M = flat[groups[gkeys[0]][0]].shape[0]
@@ -244,7 +260,9 @@ def read_torchscript_params(pt_path: str):
                 per_s.append(layers)
             weights.append(per_s)
     dims = [[aev_len] + [W.shape[0] for (W, _) in weights[0][s]] for s in range(S)]
-    rep = any("rep_calc" in k or "repulsion" in k.lower() for k in flat)
+    # The reference always stores a `use_repulsion` bool AND a dummy `rep_calc = RepulsionXTB(("H"))` submodule, also when the
+    # term is off (models/lammps_ani.py:91-99): only the VALUE of the top-level attribute says whether it is used.
+    rep = bool(flat.get("use_repulsion", False))
     p = AniParams(symbols, consts["Rcr"], consts["Rca"], float(consts["EtaR"][0]), float(consts["EtaA"][0]),
                   float(consts["Zeta"][0]), consts["ShfR"], consts["ShfA"], consts["ShfZ"], sae, dims, weights,
                   use_repulsion=bool(rep))

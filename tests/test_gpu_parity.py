@@ -285,3 +285,35 @@ def test_padded_neighbor_table_is_bit_identical_to_flat_list(ANI, ani1xnr_path, 
     assert out[0] == ref[0]
     assert np.array_equal(out[2], ref[2])
     assert np.abs(out[1] - ref[1]).max() < 1e-9             # force atomics are order-dependent in the last bits
+
+
+@pytest.mark.parametrize("x_is_float,f_is_float", [(0, 0), (1, 0), (0, 1), (1, 1)])
+def test_compute_device_matches_oracle(ANI, ani2x_synth_path, x_is_float, f_is_float):
+    """The device-tensor entry (`ANI::compute` tensor overload, ani.cpp:268-316 -> ani_compute_device): x, f and eatom are
+    device arrays, f and eatom are ACCUMULATED into (`f +=`, pair_ani_kokkos.cpp:190-191), in both Kokkos precisions."""
+    import torch
+    x, sp, box = domain.make_water_box((6, 6, 6), seed=13)
+    sub, il, nn, jl = periodic_system(x, sp, box)
+    ref = OracleANI(ani2x_synth_path).compute_full(sub.species, sub.x, il, nn, jl, sub.nlocal, single_coords=True)
+    ani = ANI(ani2x_synth_path, 0, -1, True, True, True)
+    ani.set_neighbors_full(sub.species, il, nn, jl, sub.nlocal)
+    dev = torch.device("cuda", 0)
+    xd = torch.tensor(sub.x, dtype=torch.float32 if x_is_float else torch.float64, device=dev)
+    f0 = torch.full((sub.x.shape[0], 3), 0.25, dtype=torch.float32 if f_is_float else torch.float64, device=dev)
+    e0 = torch.full((sub.nlocal,), 1.5, dtype=torch.float64, device=dev)
+    f, ea = f0.clone(), e0.clone()
+    torch.cuda.synchronize()
+    e, vir = ani.compute_device(xd.data_ptr(), bool(x_is_float), f.data_ptr(), bool(f_is_float), ea.data_ptr(), want_energy=True,
+                                want_virial=True)
+    ani.synchronize()
+    df = (f - f0).double().cpu().numpy()
+    dea = (ea - e0).cpu().numpy()
+    assert abs(e - ref["energy"]) <= E_RTOL_FP32 * abs(ref["energy"])
+    assert np.abs(df - ref["forces"]).max() <= F_TOL_FP32 + (2e-5 if f_is_float else 0.0)   # + fp32 rounding of 0.25 + f
+    assert np.abs(dea - ref["eatom"]).max() <= 1e-5 * np.abs(ref["eatom"]).max()
+    assert np.abs(vir - ref["virial"]).max() <= 1e-4 * max(1.0, np.abs(ref["virial"]).max())
+    # a second call without energy / virial (the off-thermo step of the device-resident styles): forces accumulate again
+    ani.compute_device(xd.data_ptr(), bool(x_is_float), f.data_ptr(), bool(f_is_float), 0, want_energy=False)
+    ani.synchronize()
+    df2 = (f - f0).double().cpu().numpy()
+    assert np.abs(df2 - 2.0 * ref["forces"]).max() <= 2 * F_TOL_FP32 + (4e-5 if f_is_float else 0.0)

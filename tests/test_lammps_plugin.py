@@ -22,10 +22,10 @@ needs_lmp = pytest.mark.skipif(not (os.path.exists(LMP) and os.path.exists(PLUGI
                                reason="LAMMPS binary / plugin not built (tools/_lmp, lammps_ani_b200/ani_plugin.so)")
 
 
-def run_lmp(tmp_path, model, *variables):
+def run_lmp(tmp_path, model, *variables, data="water30.data", script="in.ani"):
     env = dict(os.environ, LD_LIBRARY_PATH=os.path.dirname(LMP) + ":" + os.environ.get("LD_LIBRARY_PATH", ""))
-    cmd = [LMP, "-in", os.path.join(CASE, "in.ani"), "-log", "none", "-var", "plugin", PLUGIN, "-var", "data_file",
-           os.path.join(CASE, "water30.data"), "-var", "ani_model_file", model]
+    cmd = [LMP, "-in", os.path.join(CASE, script), "-log", "none", "-var", "plugin", PLUGIN, "-var", "data_file",
+           os.path.join(CASE, data), "-var", "ani_model_file", model]
     for k, v in variables:
         cmd += ["-var", k, str(v)]
     return subprocess.run(cmd, cwd=tmp_path, env=env, capture_output=True, text=True, timeout=600)
@@ -65,6 +65,53 @@ def _dump_forces(path):
     return frames
 
 
+NKTV2P = 68568.415          # LAMMPS `units real`: pressure [atm] = nktv2p * energy [kcal/mol] / volume [A^3]  (update.cpp)
+
+
+def _box_of(data_file):
+    lo, hi = np.zeros(3), np.zeros(3)
+    with open(os.path.join(CASE, data_file)) as fh:
+        for line in fh:
+            f = line.split()
+            for d, tag in enumerate(("xlo", "ylo", "zlo")):
+                if len(f) >= 4 and f[2] == tag:
+                    lo[d], hi[d] = float(f[0]), float(f[1])
+            if line.startswith("Atoms"):
+                break
+    return lo, hi
+
+
+def check_frame_against_oracle(orc, fr, th_row, lo, hi, single, cutoff=7.1):
+    """One dumped frame (id type x y z fx fy fz, sorted by id) + its thermo row (step pe ke etotal pxx pyy pzz pxy pxz pyz)
+    against the oracle on the same coordinates: energy, forces with the ghost forces folded back, and the pair virial
+    LAMMPS reports as c_press_pair (pair_ani.cpp:224-231: xx, yy, zz, xy, xz, yz)."""
+    L = hi - lo
+    x, sp = fr[:, 2:5], fr[:, 1].astype(np.int32) - 1
+    xw = x - lo
+    xw = xw - np.floor(xw / L) * L
+    sub = domain.decompose(xw, sp, L, cut=cutoff)[0]
+    il, nn, jl = domain.full_neighbor_list(sub.x, sub.nlocal, cut=cutoff)
+    ref = orc.compute_full(sub.species, sub.x, il, nn, jl, sub.nlocal, single_coords=single)
+    f_ref = domain.fold_ghost_forces(sub, ref["forces"])
+    f_ref_by_id = np.empty_like(f_ref)
+    f_ref_by_id[sub.global_id[:sub.nlocal]] = f_ref
+    pe = th_row[1]
+    vol = float(np.prod(L))
+    W = ref["virial"]
+    p_ref = np.array([W[0, 0], W[1, 1], W[2, 2], W[0, 1], W[0, 2], W[1, 2]]) * NKTV2P / vol
+    p_lmp = th_row[4:10]
+    pscale = max(1.0, np.abs(p_ref).max())
+    if single:
+        assert abs(pe - ref["energy"]) <= 1e-6 * abs(ref["energy"])
+        assert np.abs(fr[:, 5:8] - f_ref_by_id).max() <= 1e-4 * EV2KCAL
+        assert np.abs(p_lmp - p_ref).max() <= 2e-4 * pscale, (p_lmp, p_ref)
+    else:
+        assert abs(pe - ref["energy"]) <= 1e-10 * abs(ref["energy"])
+        assert np.abs(fr[:, 5:8] - f_ref_by_id).max() <= 1e-8
+        assert np.abs(p_lmp - p_ref).max() <= 1e-9 * pscale, (p_lmp, p_ref)
+    return ref
+
+
 @pytest.mark.gpu
 @needs_lmp
 @pytest.mark.parametrize("nbr,prec", [("full", "single"), ("half", "double"), ("full", "double"), ("device", "single"),
@@ -75,24 +122,54 @@ def test_lammps_run_matches_oracle(tmp_path, ani1xnr_path, nbr, prec):
     th = _thermo(r.stdout)
     frames = _dump_forces(os.path.join(tmp_path, "dump.forces"))
     assert th.shape[0] == 5 and len(frames) == 5
-    single = prec == "single"
     orc = OracleANI(ani1xnr_path)
+    lo, hi = _box_of("water30.data")
     for step in (0, 4):                       # step 0: fresh list; step 4: after two rebuilds and four NVE updates
-        fr = frames[step]
-        x, sp = fr[:, 2:5], fr[:, 1].astype(np.int32) - 1
-        xw = x - np.floor((x + 4.0) / 8.0) * 8.0 + 4.0         # wrap into [0, 8)
-        sub = domain.decompose(xw, sp, np.array([8.0, 8.0, 8.0]))[0]
-        il, nn, jl = domain.full_neighbor_list(sub.x, sub.nlocal)
-        ref = orc.compute_full(sub.species, sub.x, il, nn, jl, sub.nlocal, single_coords=single)
-        f_ref = domain.fold_ghost_forces(sub, ref["forces"])
-        f_ref_by_id = np.empty_like(f_ref)
-        f_ref_by_id[sub.global_id[:sub.nlocal]] = f_ref
-        pe = th[step, 1]
-        if single:
-            assert abs(pe - ref["energy"]) <= 1e-6 * abs(ref["energy"])
-            assert np.abs(fr[:, 5:8] - f_ref_by_id).max() <= 1e-4 * EV2KCAL
-        else:
-            assert abs(pe - ref["energy"]) <= 1e-10 * abs(ref["energy"])
-            assert np.abs(fr[:, 5:8] - f_ref_by_id).max() <= 1e-8
+        check_frame_against_oracle(orc, frames[step], th[step], lo, hi, prec == "single")
     # NVE over 4 x 0.1 fs: total energy conserved to the integrator's accuracy
     assert abs(th[4, 3] - th[0, 3]) < 5e-3
+
+
+@pytest.mark.gpu
+@needs_lmp
+@pytest.mark.parametrize("nbr,prec", [("full", "single"), ("device", "single"), ("half", "double")])
+def test_alanine_dipeptide_config3(tmp_path, ani2x_synth_path, nbr, prec):
+    """BASELINE.json config 3: the reference's solvated alanine dipeptide (examples/alanine-dipeptide/alanine-dipeptide.data,
+    1 912 atoms: H 1 272, O 632, C 6, N 2 -- buckets of 6 and 2 atoms, 384 active AEV columns) through the LAMMPS plugin, all 8
+    members, 4 NVE steps; ANI-2x geometry with seeded weights (the trained parameters are not available offline), the oracle
+    evaluating the very same numbers."""
+    if not os.path.exists(os.path.join(CASE, "alanine-dipeptide.data")):
+        pytest.skip("fixture not generated (tools/make_golden.py)")
+    r = run_lmp(tmp_path, ani2x_synth_path, ("ani_neighbor", nbr), ("ani_precision", prec), ("steps", 4), data="alanine-dipeptide.data")
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    th = _thermo(r.stdout)
+    frames = _dump_forces(os.path.join(tmp_path, "dump.forces"))
+    assert th.shape[0] == 5 and len(frames) == 5 and frames[0].shape[0] == 1912
+    orc = OracleANI(ani2x_synth_path)
+    lo, hi = _box_of("alanine-dipeptide.data")
+    for step in (0, 4):
+        check_frame_against_oracle(orc, frames[step], th[step], lo, hi, prec == "single")
+
+
+@pytest.mark.gpu
+@needs_lmp
+@pytest.mark.parametrize("nbr,prec", [("full", "single"), ("half", "double")])
+def test_restart_round_trip(tmp_path, ani1xnr_path, nbr, prec):
+    """write_restart -> clear -> read_restart -> pair_coeff * * -> run 0 (examples/water/README.md:51-66; the restart record of
+    pair_ani.cpp:408-455, exercised by LAMMPS's own test_pair_style.cpp:426-437): the restarted run reproduces energy, forces
+    and pressure of the run that wrote the file, and the pair style comes back with the same settings."""
+    r = run_lmp(tmp_path, ani1xnr_path, ("ani_neighbor", nbr), ("ani_precision", prec), ("steps", 2), script="in.restart")
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    th = _thermo(r.stdout)
+    frames = _dump_forces(os.path.join(tmp_path, "dump.forces")) + _dump_forces(os.path.join(tmp_path, "dump.restart"))
+    assert th.shape[0] == 4 and len(frames) == 4       # steps 0, 1, 2 of the first run + step 2 again after the restart
+    a, b = th[2], th[3]
+    tol = 1e-6 if prec == "single" else 1e-12
+    assert abs(a[1] - b[1]) <= tol * abs(a[1])
+    assert np.abs(a[4:10] - b[4:10]).max() <= max(tol, 1e-9) * max(1.0, np.abs(a[4:10]).max()) * 100
+    ftol = 1e-4 * EV2KCAL if prec == "single" else 1e-8
+    assert np.abs(frames[2][:, 5:8] - frames[3][:, 5:8]).max() <= ftol
+    assert np.abs(frames[2][:, 2:5] - frames[3][:, 2:5]).max() <= 1e-9
+    orc = OracleANI(ani1xnr_path)
+    lo, hi = _box_of("water30.data")
+    check_frame_against_oracle(orc, frames[3], th[3], lo, hi, prec == "single")

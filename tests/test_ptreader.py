@@ -56,12 +56,25 @@ class _Stacked(torch.nn.Module):
             self.layers.append(m)
 
 
+class _Rep(torch.nn.Module):
+    """Stand-in for the dummy RepulsionXTB(("H")) every exported LammpsANI carries (models/lammps_ani.py:91-99)."""
+    def __init__(self):
+        super().__init__()
+        self.register_buffer("y_ab", torch.ones(1, 1))
+        self.register_buffer("sqrt_alpha_ab", torch.ones(1, 1))
+        self.cutoff: float = 5.1
+
+
 class _Top(torch.nn.Module):
-    def __init__(self, p, stacked):
+    def __init__(self, p, stacked, use_repulsion=False):
         super().__init__()
         self.aev_computer = _AEV(p)
         self.energy_shifter = _Shifter(p)
-        if stacked:
+        self.use_repulsion: bool = use_repulsion
+        self.rep_calc = _Rep()
+        if stacked == "dict":      # BmmEnsemble container keyed by element symbol: archive order is NOT alphabetical order
+            self.neural_networks = torch.nn.ModuleDict({sym: _Stacked(p, s) for s, sym in enumerate(p.symbols)})
+        elif stacked:
             self.neural_networks = torch.nn.ModuleList([_Stacked(p, s) for s in range(p.num_species)])
         else:
             self.neural_networks = torch.nn.ModuleList(
@@ -71,7 +84,7 @@ class _Top(torch.nn.Module):
         return self.energy_shifter(self.aev_computer(x))
 
 
-@pytest.mark.parametrize("stacked", [False, True])
+@pytest.mark.parametrize("stacked", [False, True, "dict"])
 def test_pt_archive_round_trip(ani1xnr_path, tmp_path, stacked):
     p = aniw.load(ani1xnr_path)
     pt = str(tmp_path / "mock.pt")
@@ -79,6 +92,7 @@ def test_pt_archive_round_trip(ani1xnr_path, tmp_path, stacked):
     q = ptreader.read_torchscript_params(pt)
     assert q.symbols == p.symbols and q.dims == p.dims and q.num_models == p.num_models
     assert (q.Rcr, q.Rca) == (p.Rcr, p.Rca)
+    assert not q.use_repulsion          # the dummy rep_calc submodule does not switch the term on
     for name in ("ShfR", "ShfA", "ShfZ"):
         assert np.allclose(getattr(q, name), getattr(p, name), rtol=1e-6)
     assert np.allclose(q.sae, p.sae)
@@ -103,3 +117,10 @@ def test_archive_code_is_never_executed(tmp_path):
         zf.writestr("evil/data.pkl", evil)
     with pytest.raises(pickle.UnpicklingError):
         ptreader.load_object_graph(z)
+
+
+def test_use_repulsion_is_read_from_the_attribute_value(ani1xnr_path, tmp_path):
+    p = aniw.load(ani1xnr_path)
+    pt = str(tmp_path / "rep.pt")
+    torch.jit.save(torch.jit.script(_Top(p, True, use_repulsion=True)), pt)
+    assert ptreader.read_torchscript_params(pt).use_repulsion

@@ -12,6 +12,10 @@
    ensemble by the CPU oracle (periodic and non-periodic, full list), so the GPU box can check the CUDA
    path against real trained weights without /root/reference.
 3. lammps_ani_b200/data/ani1x_nr.aniw -- extracted ANI-1xnr parameters (git-ignored, ships with gpurun).
+4. tests/lammps/alanine-dipeptide.data -- BASELINE.json config 3's input, the reference's
+   examples/alanine-dipeptide/alanine-dipeptide.data (1 912 atoms) as a test fixture: atom lines verbatim, the
+   all-zero "xy xz yz" tilt line dropped so LAMMPS reads an orthogonal box (the reference's in.lammps keeps it
+   triclinic with zero tilt, which is the same geometry).
 """
 import json
 import os
@@ -107,5 +111,58 @@ def main():
     print("oracle goldens written; E(nonperiodic) =", out["cases"][0]["energy"], " E(periodic) =", out["cases"][1]["energy"])
 
 
+def test_model_header():
+    """tools/test_model_golden.h: the vectors of the C++ known-answer driver tools/test_model.cpp (the reference's
+    src/ani_csrc/test_model.cpp:84-137 inputs + ANI-2x expectations, and the oracle's ANI-1xnr results on the same inputs)."""
+    gold = os.path.join(ROOT, "tests", "golden")
+    ref = json.load(open(os.path.join(gold, "water30_reference.json")))
+    # the driver constructs ANI with use_cuaev = false like test_model.cpp:83: the half list is consumed WITHOUT a radial
+    # re-filter (SURVEY.md note N3), so the ANI-1xnr expectation is the oracle in that mode
+    from oracle.oracle import OracleANI
+    orc = OracleANI(os.path.join(ROOT, "lammps_ani_b200", "data", "ani1x_nr.aniw"))
+    r = orc.compute_half(np.array(ref["species"], dtype=np.int32), np.array(ref["coords"]).reshape(-1, 3),
+                         np.array(ref["atom_index12"]).reshape(2, -1), 30, radial_filter=False)
+    case = {"forces": r["forces"].tolist(), "energy": r["energy"]}
+
+    def arr(name, typ, vals, fmt):
+        body = ", ".join(fmt % v for v in vals)
+        return f"static const {typ} {name}[{len(vals)}] = {{{body}}};\n"
+    out = ["// GENERATED by tools/make_golden.py -- do not edit.  Inputs and ANI-2x expectations: the reference's known-answer test",
+           "// (src/ani_csrc/test_model.cpp:84-137); ANI-1xnr expectations: oracle/ani_oracle.c on the same inputs (fp64).",
+           "#pragma once", "#include <cstdint>", ""]
+    txt = "\n".join(out) + "\n"
+    txt += arr("kCoords", "double", ref["coords"], "%.17g")
+    txt += arr("kSpecies", "int", ref["species"], "%d")
+    txt += arr("kAtomIndex12", "int64_t", ref["atom_index12"], "%d")
+    txt += arr("kAni2xForce", "double", ref["test_model"]["expected_force_kcalmol_A"], "%.17g")
+    txt += "static const double kAni2xEnergyHartree = %.17g;\n" % ref["test_model"]["expected_energy_hartree"]
+    txt += arr("kAni1xnrForce", "double", np.array(case["forces"]).reshape(-1).tolist(), "%.17g")
+    txt += "static const double kAni1xnrEnergyKcalmol = %.17g;\n" % case["energy"]
+    with open(os.path.join(ROOT, "tools", "test_model_golden.h"), "w") as f:
+        f.write(txt)
+    print("wrote tools/test_model_golden.h")
+
+
+def alanine_fixture():
+    src = os.path.join(REF, "examples/alanine-dipeptide/alanine-dipeptide.data")
+    dst = os.path.join(ROOT, "tests", "lammps", "alanine-dipeptide.data")
+    lines = open(src).read().splitlines()
+    out = ["# solvated alanine dipeptide, 1912 atoms: test fixture generated by tools/make_golden.py from the reference's "
+           "examples/alanine-dipeptide/alanine-dipeptide.data"]
+    for ln in lines[1:]:
+        f = ln.split()
+        if len(f) >= 6 and f[3:6] == ["xy", "xz", "yz"]:
+            assert all(float(v) == 0.0 for v in f[:3])
+            continue
+        if "bond" in ln:
+            continue
+        out.append(ln.split("#")[0].rstrip() if len(f) >= 5 and f[0].isdigit() else ln)
+    with open(dst, "w") as fh:
+        fh.write("\n".join(out) + "\n")
+    print("wrote", dst)
+
+
 if __name__ == "__main__":
     main()
+    alanine_fixture()
+    test_model_header()
