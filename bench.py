@@ -11,8 +11,14 @@ ANI-2x geometry (7 species, 1008-long AEV), all 8 ensemble members, fp32, full n
 weak-scaled the way the reference does it (`replicate`: one identical replica per rank, brick grid 1x1x1 /
 2x1x1 / 2x2x1 / 2x2x2).  ANI-2x weights are not available offline: seeded random weights of the ANI-2x shapes
 (throughput does not depend on the values).  A step = forward halo (ghost positions) -> AEV -> ensemble MLP
-fwd+bwd -> force/virial scatter -> reverse halo (ghost forces); coordinates are static, the neighbour list is
-uploaded once (LAMMPS re-uploads it every ~10 steps; that rebuild is outside this path).
+fwd+bwd -> force/virial scatter -> reverse halo (ghost forces).
+
+Three numbers per run (config.workload says which is which):
+  value     the pair path on static coordinates with the list installed once (the hot path of BASELINE.json's north_star);
+  value_md  the reference's benchmark protocol (examples/benchmark/in.lammps:24-26,53-59) with everything on the device: fix nve +
+            fix langevin (library kernels), moving coordinates, the neighbour list rebuilt on the device every 10 steps INSIDE the
+            timed region -- the quantity LAMMPS's "Loop time" measures;
+  e2e       the reference-facing host call (ani_compute, host buffers, H2D + D2H inside the timed region).
 """
 from __future__ import annotations
 
@@ -36,14 +42,15 @@ DT_FS = 0.5
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=100)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--atoms", type=int, default=int(os.environ.get("ANI_BENCH_ATOMS", 300000)), help="atoms per GPU")
     ap.add_argument("--models", type=int, default=8)
     ap.add_argument("--mlp-mode", default=os.environ.get("ANI_B200_MLP_MODE", ""), help="simt | tf32x3 | tf32 | f16x3 (default: the library default, f16x3)")
     ap.add_argument("--cpu-sample-atoms", type=int, default=0)
-    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-cpu-baseline", action="store_true", default=bool(os.environ.get("ANI_BENCH_NO_CPU")))
+    ap.add_argument("--no-md", action="store_true", help="skip the MD leg (value_md)")
     return ap.parse_args()
 
 
@@ -156,6 +163,63 @@ def cpu_baseline(model, sub, il, nn, jl, M, sample_atoms, repeats=1):
         dt = time.perf_counter() - t0
         best = dt if best is None else min(best, dt)
     return S / best, S, ncores, best
+
+
+def kernel_source_hash():
+    """Short hash of the MLP / AEV kernel sources: names the ncu capture a traffic figure may be quoted from (the GPU box has no
+    .git, so the commit id cannot be used)."""
+    import hashlib
+    h = hashlib.sha1()
+    for f in ("mlp_f16_fused.cuh", "mlp_f16.cuh", "aev2.cuh"):
+        with open(os.path.join(ROOT, "lammps_ani_b200", "csrc", f), "rb") as fh:
+            h.update(fh.read())
+    return h.hexdigest()[:10]
+
+
+def measured_traffic(nlocal):
+    """DRAM bytes per step of the MLP stage from an `ncu --set full` capture of THIS kernel source and THIS workload size:
+    profiles/*_<source hash>_<nlocal>_raw.csv (written by tools/ncu_traffic.py from the .ncu-rep).  None when there is no such
+    capture -- a figure from another build must not be quoted."""
+    import csv
+    import glob
+    tag = kernel_source_hash()
+    for path in sorted(glob.glob(os.path.join(ROOT, "profiles", f"*_{tag}_{nlocal}_raw.csv"))):
+        try:
+            rows = list(csv.reader(open(path)))
+            hdr = rows[0]
+            kn, rd, wr = hdr.index("Kernel Name"), hdr.index("dram__bytes_read.sum"), hdr.index("dram__bytes_write.sum")
+            unit_r, unit_w = rows[1][rd], rows[1][wr]
+            scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+            tot, seen = 0.0, {}
+            for r in rows[2:]:
+                if "f16_fused" in r[kn] or "f16_gemm" in r[kn]:
+                    seen.setdefault(r[kn], []).append(float(r[rd]) * scale[unit_r] + float(r[wr]) * scale[unit_w])
+            # the capture holds whole steps: the launches of one step = one entry per bucket launch; average over the steps captured
+            per_step = sum(sum(v) for v in seen.values())
+            steps = json.load(open(path.replace("_raw.csv", "_meta.json"))).get("steps_captured", 1) if os.path.exists(path.replace("_raw.csv", "_meta.json")) else 1
+            return per_step / max(steps, 1), os.path.basename(path)
+        except Exception:
+            continue
+    return None, None
+
+
+def cpu_baseline_torch(model, M, cells=(16, 16, 16)):
+    """the torch-CPU pyaev restatement (oracle/pyaev_torch.py: half pair list, pair/triple tensor formulation,
+    autograd -- the closest thing to what the reference's `device cpu` path executes), all host threads, on a periodic water
+    box of the same density and list radius (12 288 atoms + ghosts by default: bounded by the memory of the triple tensors)."""
+    import torch
+    from lammps_ani_b200 import aniw, domain
+    from oracle.pyaev_torch import pyaev_forward
+    params = aniw.load(model)
+    ncores = os.cpu_count() or 1
+    torch.set_num_threads(ncores)
+    x, sp, box = domain.make_water_box(cells, seed=12345)
+    sub = domain.decompose(x, sp, box)[0]
+    idx = domain.half_neighbor_list(sub.x, sub.nlocal)
+    t0 = time.perf_counter()
+    pyaev_forward(params, sub.species, sub.x, idx, sub.nlocal, num_models=M)
+    dt = time.perf_counter() - t0
+    return sub.nlocal / dt, sub.nlocal, ncores, dt
 
 
 def run_reference(args):
@@ -301,13 +365,51 @@ def main():
     torch.cuda.synchronize()
     rebuild_host_ms = (time.perf_counter() - t0) * 1e3
     assert npairs_dev == int(jl.size), "device-built list differs from the host list"
+    # ---------------- multi-GPU force check: identical replicas make the N-rank answer equal to the single periodic domain's
+    force_check = None
+    if world > 1:
+        step.step_gpu()
+        f_multi = step.f[:nlocal].clone()
+        step.step_local_periodic(lambda s: s.pair_compute(False))
+        f_single = step.f[:nlocal]
+        dmax = float((f_multi - f_single).abs().max())
+        t = torch.tensor([dmax], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dmax = float(t[0])
+        assert dmax <= 1e-4 * 23.060548, f"forces through the {world}-rank halo exchange differ from the periodic single-domain result by {dmax} kcal/mol/A"
+        force_check = {"status": "ok", "max_abs_diff_kcal_mol_A": dmax, "tolerance": 1e-4 * 23.060548,
+                       "what": "local forces after the NCCL ghost exchange vs the same rank's single periodic domain (ghosts served locally)"}
+    # ---------------- MD leg (value_md): the reference's benchmark protocol on the device -- fix nve + fix langevin (300 K, damp
+    # 100 fs), dt 0.5 fs, moving coordinates, list rebuilt on the device every 10 steps inside the timed region
+    ms_md, md_info = None, None
+    if not args.no_md:
+        from lammps_ani_b200 import nve
+        masses = np.array([nve.MASS[params.symbols[int(sidx)]] for sidx in sub.species[:nlocal]])
+        md = nve.DeviceNVE(step, masses, DT_FS, temperature=300.0, seed=12345, rebuild_every=10, langevin_damp_fs=100.0)
+        for _ in range(10):
+            md.advance()
+        nmd = max(10, args.steps // 10 * 10)
+        barrier()
+        m0, m1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        r0 = md.rebuilds
+        m0.record()
+        for _ in range(nmd):
+            md.advance()
+        m1.record()
+        barrier()
+        ms_md = m0.elapsed_time(m1)
+        ke = md.kinetic()
+        md_info = {"steps": nmd, "rebuilds_in_timed_region": md.rebuilds - r0, "dt_fs": DT_FS,
+                   "temperature_K_after": 2.0 * ke / (3.0 * nlocal * nve.BOLTZ),
+                   "protocol": "fix nve + fix langevin 300 300 100 (uniform noise) as library kernels, neigh_modify every 10 (device rebuild), "
+                               "examples/benchmark/in.lammps:24-26,53-59"}
     # ---------------- reduce over ranks (max time)
-    tm = torch.tensor([ms, ms_e2e], dtype=torch.float64, device=dev)
+    tm = torch.tensor([ms, ms_e2e, (ms_md or 0.0) / (md_info["steps"] if md_info else 1)], dtype=torch.float64, device=dev)
     cnt = torch.tensor([float(nlocal)], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(tm, op=dist.ReduceOp.MAX)
         dist.all_reduce(cnt, op=dist.ReduceOp.SUM)
-    ms, ms_e2e = float(tm[0]), float(tm[1])
+    ms, ms_e2e, ms_md_step = float(tm[0]), float(tm[1]), float(tm[2])
     natoms_total = float(cnt[0])
     value = natoms_total * args.steps / (ms * 1e-3)
     value_e2e = natoms_total * args.steps / (ms_e2e * 1e-3)
@@ -332,13 +434,14 @@ def main():
         L = Lc
         aev_bytes = nlocal * (4.0 * float(jl.size) / nlocal + 8 + 16 + 4 * L)       # list + x + AEV row store
         bwd_bytes = nlocal * (4.0 * L + 4.0 * float(jl.size) / nlocal + 16 + 12)
-        roofline = {"kernel": f"ensemble MLP fwd+bwd GEMM stage ({mode})", "bound": "tensor", "achieved": ach,
-                    "peak": tf32_peak, "unit": "TFLOP/s", "frac": ach / tf32_peak,
-                    # dram__bytes_read + write summed over the stage's 12 GEMM launches of one step, ncu capture of this
-                    # workload (profiles/r1_launches_final_300k.csv); null for other sizes / modes
-                    "traffic": 23.2e9 if (args.mlp_mode in ("", "f16x3") and abs(nlocal - 299538) < 10 and M == 8) else None,
-                    "traffic_note": "per step over the stage's launches; 5.2 TB/s = 81 % of the measured HBM peak: the stage is "
-                                    "bound by its own fp16 hi/lo intermediates (10.2 KB per atom-member), not by the tensor pipe",
+        traffic, traffic_src = measured_traffic(nlocal) if (args.mlp_mode in ("", "f16x3") and M == 8) else (None, None)
+        roofline = {"kernel": f"ensemble MLP fwd+bwd stage ({mode}; one fused kernel per species bucket: f16_fused_kernel)", "bound": "tensor",
+                    "achieved": ach, "peak": tf32_peak, "unit": "TFLOP/s", "frac": ach / tf32_peak,
+                    # dram__bytes_read + write over the stage's launches of one step, parsed from the ncu capture of exactly this
+                    # kernel source (hash) and workload size; null when no such capture is committed
+                    "traffic": traffic, "traffic_source": traffic_src, "kernel_source_hash": kernel_source_hash(),
+                    "traffic_note": "DRAM bytes per step over the MLP stage's launches (ncu --set full); the algorithmic I/O of the stage is "
+                                    "1 KB per atom with 128 active AEV columns (AEV planes in, dE/dAEV out)",
                     "peak_source": (f"{which}: bf16_tflops_sustained (fp16 runs at the bf16 rate)" if args.mlp_mode == "f16x3"
                                     else f"{which}: bf16_tflops_sustained/2 taken as the dense TF32 peak"),
                     "issued_flops_factor": passes, "frac_issued": passes * ach / tf32_peak,
@@ -364,7 +467,8 @@ def main():
             "config": {"workload": f"examples/water-style periodic water box, {nlocal} atoms + {ntotal - nlocal} ghosts per GPU "
                                    f"(lattice {cells[0]}x{cells[1]}x{cells[2]} molecules), ANI-2x geometry (1008 AEV, 7 species; {Lc} columns active for the species present), "
                                    f"{M} ensemble members, fp32, full neighbour list 7.1 A ({jl.size / nlocal:.1f}/atom), "
-                                   f"replicate grid {grid[0]}x{grid[1]}x{grid[2]}",
+                                   f"replicate grid {grid[0]}x{grid[1]}x{grid[2]}; `value` = pair path on static coordinates, list "
+                                   f"installed once; `value_md` = nve + langevin + device rebuild every 10 steps inside the timed region",
                        "weights": "seeded random, ANI-2x shapes (real ANI-2x parameters unavailable offline)",
                        "mlp_mode": mode, "l2": "inputs larger than L2 (AEV rows alone exceed 126 MB); no explicit flush",
                        "vs_baseline_note": "published number is 1xA100, Kokkos, 300k water, 8 models (BASELINE.md)",
@@ -375,16 +479,33 @@ def main():
                     "path": "ani_compute (C ABI, host pointers): host x[ntotal] f64 -> device (DMA from the caller's array, "
                             "page-locked in place once it is seen at a stable address), AEV+MLP+force scatter, f widened to "
                             "f64 on the device -> DMA into the caller's out_force + energy; ghosts supplied by the caller "
-                            "as LAMMPS does"},
+                            "as LAMMPS does",
+                    "halo": False if world > 1 else None,
+                    "halo_note": ("N independent host calls: the caller (LAMMPS's CommBrick) supplies ghost positions and folds ghost "
+                                  "forces; the NCCL exchange is part of `value` / `value_md` only") if world > 1 else None},
             "gpu_launches": int(launches) * args.steps, "gpu_launches_per_step": int(launches),
             "clocks": clocks, "roofline": roofline, "stages": stages,
         }
+        if md_info is not None:
+            line["value_md"] = natoms_total / (ms_md_step * 1e-3)
+            line["ms_per_step_md"] = ms_md_step
+            line["md"] = md_info
+        if force_check is not None:
+            line["multi_gpu_force_check"] = force_check["status"]
+            line["multi_gpu_force_check_detail"] = force_check
         if not args.no_cpu_baseline and world == 1:
             rate, S0, ncores, dt = cpu_baseline(model, sub, il, nn, jl, M, 256)
             S = args.cpu_sample_atoms or int(max(256, min(nlocal, rate * 12.0)))
             rate, S, ncores, dt = cpu_baseline(model, sub, il, nn, jl, M, S)
             line["cpu_baseline"] = {"value": rate, "unit": "atom-timesteps/s", "cores": ncores, "kind": "port",
                                     "sample": f"{S} centre atoms of the same box, one pass ({dt:.1f} s), oracle/ani_oracle.c OpenMP fp64"}
+            try:
+                r2, S2, nc2, dt2 = cpu_baseline_torch(model, M)
+                line["cpu_baseline_torch"] = {"value": r2, "unit": "atom-timesteps/s", "cores": nc2, "kind": "port",
+                                              "sample": f"{S2}-atom periodic water box (same density, 7.1 A half list), one pass ({dt2:.1f} s), oracle/pyaev_torch.py "
+                                                        f"(pair/triple tensors + autograd, fp64, torch {nc2} threads): SURVEY.md 8d (i)"}
+            except Exception as err:      # a reported baseline, never a reason to lose the bench line
+                line["cpu_baseline_torch"] = {"unavailable": str(err)[:200]}
         print(json.dumps(line))
     if world > 1:
         dist.barrier()

@@ -133,6 +133,27 @@ int ani_halo_pack_x(ani_ctx* ctx, const void* x_dev, int is_float, const int64_t
 int ani_halo_unpack_add_f(ani_ctx* ctx, void* f_dev, int is_float, const int64_t* index_dev, const void* buf_dev,
                           int64_t n);
 
+/* ---- device-resident time integration: what `modify->initial_integrate / post_force / final_integrate`
+ * do on the host around the pair compute in the reference's run loop (external/lammps/src/verlet.cpp:253-256,347-349), so
+ * that x, v, f stay on the GPU between neighbour rebuilds.  All arrays are DEVICE pointers, [n][3] doubles, mass_dev[n] per
+ * atom; the kernels run on the context's stream.  Unit factors are the caller's (LAMMPS: dtv = dt, dtf = 0.5 dt ftm2v).
+ *   ani_md_nve_initial : v += dtf f / m ; x += dtv v              (fix_nve.cpp FixNVE::initial_integrate)
+ *   ani_md_nve_final   : v += dtf f / m                           (FixNVE::final_integrate)
+ *   ani_md_langevin    : f += -m g1 v + sqrt(m) g2 (u - 0.5), u uniform on [0,1)   (fix_langevin.cpp post_force, the default
+ *                        uniform-noise variant; g1 = 1/t_period/ftm2v, g2 = sqrt(24 boltz/t_period/dt/mvv2e)/ftm2v*sqrt(T));
+ *                        u is a counter-based hash of (seed, step, tag[i] or i, component): independent of the decomposition
+ *   ani_md_sum_mv2     : sum_i m_i |v_i|^2 to the host (kinetic energy / temperature on thermo steps; synchronises)
+ *   ani_md_ghost_x     : x[nlocal+g] = x[owner[g]] + shift[g]    (forward_comm of a single periodic domain, comm_brick.cpp:549-593)
+ *   ani_md_fold_ghost_f: f[owner[g]] += f[nlocal+g]               (reverse_comm(Pair*), pair_ani.cpp:197-201,461-484)          */
+int ani_md_nve_initial(ani_ctx* ctx, double* x_dev, double* v_dev, const double* f_dev, const double* mass_dev, int n,
+                       double dtv, double dtf);
+int ani_md_nve_final(ani_ctx* ctx, double* v_dev, const double* f_dev, const double* mass_dev, int n, double dtf);
+int ani_md_langevin(ani_ctx* ctx, const double* v_dev, double* f_dev, const double* mass_dev, const int64_t* tag_dev, int n,
+                    double g1, double g2, uint64_t seed, int64_t step);
+int ani_md_sum_mv2(ani_ctx* ctx, const double* v_dev, const double* mass_dev, int n, double* out_host);
+int ani_md_ghost_x(ani_ctx* ctx, double* x_dev, const int* owner_dev, const double* shift_dev, int nlocal, int nghost);
+int ani_md_fold_ghost_f(ani_ctx* ctx, double* f_dev, const int* owner_dev, int nlocal, int nghost);
+
 /* ---- introspection for tests, profiling and bench ------------------------------------------------------- */
 /* Copy the AEV rows / dE/dAEV rows of the local atoms (atom order, [nlocal][aev_length] doubles) of the
  * last compute to host memory. */

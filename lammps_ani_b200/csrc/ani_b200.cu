@@ -21,6 +21,7 @@
 #include "mlp_f16_fused.cuh"
 #include "mlp_tc.cuh"
 #include "nbuild.cuh"
+#include "md.cuh"
 
 namespace anib {
 
@@ -112,8 +113,10 @@ struct UserPin {
 
 struct EngineBase {
   virtual ~EngineBase() {}
+  // csr_dev_maxnn >= 0: beg_h / cnt_h are DEVICE arrays (already the engine's own d_beg / d_cnt or to be copied device to device)
+  // and the value is the longest row; < 0: host arrays
   virtual int set_neighbors(int nlocal, int ntotal, const int* species_h, const int64_t* beg_h, const int* cnt_h,
-                            const int* jlist, int64_t npairs, bool jlist_on_device) = 0;
+                            const int* jlist, int64_t npairs, bool jlist_on_device, int csr_dev_maxnn = -1) = 0;
   virtual int compute(const void* x, bool x_on_device, bool x_is_float, double* out_energy, double* out_force_host,
                       void* f_dev, bool f_is_float, double* out_eatom_host, double* eatom_dev, double* out_virial9) = 0;
   virtual int get_aev(double* aev, double* daev) = 0;
@@ -181,7 +184,8 @@ struct Engine : EngineBase {
   std::vector<int> boff;   // bucket offsets [S+1] (rows of species s = [boff[s], boff[s+1]))
   std::vector<int> h_order, h_cspecies;
   DevBuf d_species, d_beg, d_cnt, d_jlist, d_order;
-  const int* jlist_ptr = nullptr;
+  const int* jlist_ext = nullptr;     // the device-built list in nb_jlist, used in place
+  const int* jl() const { return jlist_ext ? jlist_ext : d_jlist.as<int>(); }
   // per-step state
   DevBuf d_xraw, d_x4, d_aev, d_daev, d_force, d_eatom, d_eatom_atom, d_partial, d_scalars, d_virial, d_err;
   DevBuf d_aev_hi, d_aev_lo;
@@ -329,7 +333,7 @@ struct Engine : EngineBase {
 
   // ---------------------------------------------------------------------------------------------- rebuild
   int set_neighbors(int nlocal_, int ntotal_, const int* species_h, const int64_t* beg_h, const int* cnt_h,
-                    const int* jlist, int64_t npairs_, bool jlist_on_device) override {
+                    const int* jlist, int64_t npairs_, bool jlist_on_device, int csr_dev_maxnn = -1) override {
     nlocal = nlocal_; ntotal = ntotal_; npairs = npairs_;
     cudaStream_t st = c->stream;
     // species bucketing (stable counting sort over local atoms) -- K4 of SURVEY.md 2.1, on rebuild only
@@ -357,21 +361,29 @@ struct Engine : EngineBase {
       std::vector<int> cur(boff.begin(), boff.end() - 1);
       for (int i = 0; i < nlocal; i++) h_order[cur[species_h[i]]++] = i;
     }
-    int maxnn = 0;
-    for (int i = 0; i < nlocal; i++) maxnn = std::max(maxnn, cnt_h[i]);
+    const bool csr_dev = csr_dev_maxnn >= 0;
+    int maxnn = csr_dev ? csr_dev_maxnn : 0;
+    if (!csr_dev)
+      for (int i = 0; i < nlocal; i++) maxnn = std::max(maxnn, cnt_h[i]);
     cap = std::max(32, (maxnn + 31) / 32 * 32);
     capA = std::min(cap, 96);
     ANIB_RESERVE(d_species, (size_t)ntotal * sizeof(int));
     ANIB_RESERVE(d_beg, (size_t)std::max(nlocal, 1) * sizeof(int64_t));
     ANIB_RESERVE(d_cnt, (size_t)std::max(nlocal, 1) * sizeof(int));
     ANIB_RESERVE(d_order, (size_t)std::max(nlocal, 1) * sizeof(int));
-    ANIB_RESERVE(d_jlist, (size_t)std::max<int64_t>(npairs, 1) * sizeof(int));
     ANIB_CUDA_OK(cudaMemcpyAsync(d_species.p, h_cspecies.data(), (size_t)ntotal * sizeof(int), cudaMemcpyHostToDevice, st));   // compact indices
-    ANIB_CUDA_OK(cudaMemcpyAsync(d_beg.p, beg_h, (size_t)nlocal * sizeof(int64_t), cudaMemcpyHostToDevice, st));
-    ANIB_CUDA_OK(cudaMemcpyAsync(d_cnt.p, cnt_h, (size_t)nlocal * sizeof(int), cudaMemcpyHostToDevice, st));
+    const cudaMemcpyKind ck = csr_dev ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
+    ANIB_CUDA_OK(cudaMemcpyAsync(d_beg.p, beg_h, (size_t)nlocal * sizeof(int64_t), ck, st));
+    ANIB_CUDA_OK(cudaMemcpyAsync(d_cnt.p, cnt_h, (size_t)nlocal * sizeof(int), ck, st));
     ANIB_CUDA_OK(cudaMemcpyAsync(d_order.p, h_order.data(), (size_t)nlocal * sizeof(int), cudaMemcpyHostToDevice, st));
-    ANIB_CUDA_OK(cudaMemcpyAsync(d_jlist.p, jlist, (size_t)npairs * sizeof(int),
-                                 jlist_on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, st));
+    if (jlist_on_device && csr_dev) {
+      jlist_ext = jlist;                          // the list the device build just wrote stays where it is (no 600 MB copy)
+    } else {
+      jlist_ext = nullptr;
+      ANIB_RESERVE(d_jlist, (size_t)std::max<int64_t>(npairs, 1) * sizeof(int));
+      ANIB_CUDA_OK(cudaMemcpyAsync(d_jlist.p, jlist, (size_t)npairs * sizeof(int),
+                                   jlist_on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, st));
+    }
     ANIB_CUDA_OK(cudaStreamSynchronize(st));   // host staging vectors may be reused by the caller
     // per-step buffers
     ANIB_RESERVE(d_x4, (size_t)std::max(ntotal, 1) * 4 * sizeof(T));
@@ -412,16 +424,20 @@ struct Engine : EngineBase {
     ANIB_RESERVE(nb_cell_s, (size_t)nt * 4); ANIB_RESERVE(nb_atom_s, (size_t)nt * 4);
     ANIB_RESERVE(nb_cbeg, (size_t)ncell * 4); ANIB_RESERVE(nb_cend, (size_t)ncell * 4);
     ANIB_RESERVE(nb_cnt, (size_t)std::max(nlocal_, 1) * 4); ANIB_RESERVE(nb_beg, (size_t)std::max(nlocal_, 1) * 8);
-    c->h_cnt.assign(std::max(nlocal_, 1), 0);
-    c->h_beg.assign(std::max(nlocal_, 1), 0);
     int64_t P = 0;
+    int maxnn = 0;
     if (ntotal_ > 0 && nlocal_ > 0) {
       nb_cell_id_kernel<<<(ntotal_ + 255) / 256, 256, 0, st>>>(xd, ntotal_, G, nb_cell.as<int>(), nb_atom.as<int>());
-      size_t tmp_bytes = 0;
+      size_t tmp_bytes = 0, scan_bytes = 0, max_bytes = 0;
       int bits = 1;
       while (((int64_t)1 << bits) < ncell) bits++;
       cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, nb_cell.as<int>(), nb_cell_s.as<int>(), nb_atom.as<int>(), nb_atom_s.as<int>(),
                                       ntotal_, 0, bits, st);
+      auto cnt64 = thrust::make_transform_iterator((const int*)nb_cnt.as<int>(), NbToI64());
+      cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, cnt64, nb_beg.as<int64_t>(), nlocal_, st);
+      ANIB_RESERVE(nb_red, 16);
+      cub::DeviceReduce::Max(nullptr, max_bytes, nb_cnt.as<int>(), (int*)nb_red.p, nlocal_, st);
+      tmp_bytes = std::max(tmp_bytes, std::max(scan_bytes, max_bytes));
       ANIB_RESERVE(nb_tmp, tmp_bytes + 16);
       ANIB_CUDA_OK(cub::DeviceRadixSort::SortPairs(nb_tmp.p, tmp_bytes, nb_cell.as<int>(), nb_cell_s.as<int>(), nb_atom.as<int>(),
                                                    nb_atom_s.as<int>(), ntotal_, 0, bits, st));
@@ -430,27 +446,34 @@ struct Engine : EngineBase {
       nb_cell_range_kernel<<<(ntotal_ + 255) / 256, 256, 0, st>>>(nb_cell_s.as<int>(), ntotal_, nb_cbeg.as<int>(), nb_cend.as<int>());
       nb_search_kernel<false><<<(nlocal_ + 127) / 128, 128, 0, st>>>(xd, nlocal_, G, nb_cbeg.as<int>(), nb_cend.as<int>(),
                                                                    nb_atom_s.as<int>(), cutoff * cutoff, nb_cnt.as<int>(), nullptr, nullptr);
-      ANIB_CUDA_OK(cudaMemcpyAsync(c->h_cnt.data(), nb_cnt.p, (size_t)nlocal_ * 4, cudaMemcpyDeviceToHost, st));
+      // CSR offsets, the total and the longest row on the device; only two scalars come back to the host
+      ANIB_CUDA_OK(cub::DeviceScan::ExclusiveSum(nb_tmp.p, tmp_bytes, cnt64, nb_beg.as<int64_t>(), nlocal_, st));
+      ANIB_CUDA_OK(cub::DeviceReduce::Max(nb_tmp.p, tmp_bytes, nb_cnt.as<int>(), (int*)nb_red.p, nlocal_, st));
+      nb_total_kernel<<<1, 1, 0, st>>>(nb_beg.as<int64_t>(), nb_cnt.as<int>(), nlocal_, (int64_t*)((char*)nb_red.p + 8));
+      ANIB_RESERVE(h_nb, 16);
+      ANIB_CUDA_OK(cudaMemcpyAsync(h_nb.p, nb_red.p, 16, cudaMemcpyDeviceToHost, st));
       ANIB_CUDA_OK(cudaStreamSynchronize(st));
-      for (int i = 0; i < nlocal_; i++) { c->h_beg[i] = P; P += c->h_cnt[i]; }   // the only host pass: nlocal integers
+      maxnn = *(const int*)h_nb.p;
+      P = *(const int64_t*)((const char*)h_nb.p + 8);
       ANIB_RESERVE(nb_jlist, (size_t)std::max<int64_t>(P, 1) * 4);
-      ANIB_CUDA_OK(cudaMemcpyAsync(nb_beg.p, c->h_beg.data(), (size_t)nlocal_ * 8, cudaMemcpyHostToDevice, st));
       nb_search_kernel<true><<<(nlocal_ + 127) / 128, 128, 0, st>>>(xd, nlocal_, G, nb_cbeg.as<int>(), nb_cend.as<int>(),
                                                                   nb_atom_s.as<int>(), cutoff * cutoff, nullptr, nb_beg.as<int64_t>(),
                                                                   nb_jlist.as<int>());
       ANIB_CUDA_OK(cudaGetLastError());
-      c->launches = 4;
+      c->launches = 7;
     }
     if (npairs_out) *npairs_out = P;
-    return set_neighbors(nlocal_, ntotal_, species_h, c->h_beg.data(), c->h_cnt.data(), nb_jlist.as<int>(), P, true);
+    return set_neighbors(nlocal_, ntotal_, species_h, nb_beg.as<int64_t>(), nb_cnt.as<int>(), nb_jlist.as<int>(), P, true, maxnn);
   }
+  DevBuf nb_red;
+  PinnedBuf h_nb;
 
   void release_pins() override { pin_x.release(); pin_f.release(); }
 
   int get_neighbors(int* numneigh, int* jlist) override {
     ANIB_CUDA_OK(cudaStreamSynchronize(c->stream));
     if (numneigh && nlocal > 0) ANIB_CUDA_OK(cudaMemcpy(numneigh, d_cnt.p, (size_t)nlocal * 4, cudaMemcpyDeviceToHost));
-    if (jlist && npairs > 0) ANIB_CUDA_OK(cudaMemcpy(jlist, d_jlist.p, (size_t)npairs * 4, cudaMemcpyDeviceToHost));
+    if (jlist && npairs > 0) ANIB_CUDA_OK(cudaMemcpy(jlist, jl(), (size_t)npairs * 4, cudaMemcpyDeviceToHost));
     return 0;
   }
 
@@ -607,7 +630,7 @@ struct Engine : EngineBase {
           const Aev2Layout L1 = aev2_layout<T>(cap1, capA1, P.aev_len, P.nZ, P.nA, false);
           rs.ovf_cnt = d_ovf.as<int>() + 2; rs.ovf_rows = d_ovf_rows.as<int>();
           kern<<<grid, kAev2Warps * 32, L1.bytes * kAev2Warps, st>>>(
-              P, c->use_cuaev ? 1 : 0, d_x4.as<V4>(), d_beg.as<int64_t>(), d_cnt.as<int>(), d_jlist.as<int>(), d_order.as<int>(),
+              P, c->use_cuaev ? 1 : 0, d_x4.as<V4>(), d_beg.as<int64_t>(), d_cnt.as<int>(), jl(), d_order.as<int>(),
               nlocal, rows, ld_aev, hi, lo, ldp, plane_mode, f16::kScaleAev, cap1, capA1, L1.bytes, d_err.as<int>(), rs);
           c->launches++;
           rs = Aev2Rows();
@@ -616,11 +639,11 @@ struct Engine : EngineBase {
         if (two_pass) {
           ANIB_CUDA_OK(cudaFuncSetAttribute(kern_strided, cudaFuncAttributeMaxDynamicSharedMemorySize, smem2));
           kern_strided<<<std::min(grid, 592), kAev2Warps * 32, smem2, st>>>(
-              P, c->use_cuaev ? 1 : 0, d_x4.as<V4>(), d_beg.as<int64_t>(), d_cnt.as<int>(), d_jlist.as<int>(), d_order.as<int>(),
+              P, c->use_cuaev ? 1 : 0, d_x4.as<V4>(), d_beg.as<int64_t>(), d_cnt.as<int>(), jl(), d_order.as<int>(),
               nlocal, rows, ld_aev, hi, lo, ldp, plane_mode, f16::kScaleAev, cap, capA, L2.bytes, d_err.as<int>(), rs);
         } else
           kern<<<grid, kAev2Warps * 32, smem2, st>>>(
-              P, c->use_cuaev ? 1 : 0, d_x4.as<V4>(), d_beg.as<int64_t>(), d_cnt.as<int>(), d_jlist.as<int>(), d_order.as<int>(),
+              P, c->use_cuaev ? 1 : 0, d_x4.as<V4>(), d_beg.as<int64_t>(), d_cnt.as<int>(), jl(), d_order.as<int>(),
               nlocal, rows, ld_aev, hi, lo, ldp, plane_mode, f16::kScaleAev, cap, capA, L2.bytes, d_err.as<int>(), rs);
         return 0;
       };
@@ -630,7 +653,7 @@ struct Engine : EngineBase {
       else if (aev_gen == 2 && P.nZ == 8 && P.nA == 8) rc2 = launch2(aev2_forward_kernel<T, 8, 8>, aev2_forward_kernel<T, 8, 8, true>);
       else
         aev_forward_kernel<T><<<(nlocal + kAevWarps - 1) / kAevWarps, kAevWarps * 32, smem, st>>>(
-            P, c->use_cuaev ? 1 : 0, d_x4.as<V4>(), d_beg.as<int64_t>(), d_cnt.as<int>(), d_jlist.as<int>(),
+            P, c->use_cuaev ? 1 : 0, d_x4.as<V4>(), d_beg.as<int64_t>(), d_cnt.as<int>(), jl(),
             d_order.as<int>(), nlocal, rows, ld_aev, hi, lo, ldp, plane_mode, f16::kScaleAev, cap, capA, Lf.bytes,
             d_err.as<int>());
       if (rc2) return rc2;
@@ -656,7 +679,7 @@ struct Engine : EngineBase {
       auto launch = [&](auto kern) -> int {
         ANIB_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
         kern<<<(nlocal + kAevWarps - 1) / kAevWarps, kAevWarps * 32, smem, st>>>(
-            P, c->use_cuaev ? 1 : 0, d_x4.as<V4>(), d_beg.as<int64_t>(), d_cnt.as<int>(), d_jlist.as<int>(),
+            P, c->use_cuaev ? 1 : 0, d_x4.as<V4>(), d_beg.as<int64_t>(), d_cnt.as<int>(), jl(),
             d_order.as<int>(), nlocal, d_daev.as<T>(), ld_aev, d_force.as<T>(),
             want_virial ? d_virial.as<double>() : nullptr, (T)kHartree2KcalMol, cap, capA, Lb.bytes);
         c->launches++;
@@ -672,7 +695,7 @@ struct Engine : EngineBase {
           const Aev2Layout L1 = aev2_layout<T>(cap1, capA1, acc_b, P.nZ, P.nA, true);
           rs.ovf_cnt = d_ovf.as<int>() + 3; rs.ovf_rows = d_ovf_rows.as<int>() + nlocal;
           kern<<<grid, kAev2Warps * 32, L1.bytes * kAev2Warps, st>>>(
-              P, c->use_cuaev ? 1 : 0, d_x4.as<V4>(), d_beg.as<int64_t>(), d_cnt.as<int>(), d_jlist.as<int>(), d_order.as<int>(),
+              P, c->use_cuaev ? 1 : 0, d_x4.as<V4>(), d_beg.as<int64_t>(), d_cnt.as<int>(), jl(), d_order.as<int>(),
               nlocal, d_daev.as<T>(), ld_aev, d_force.as<T>(), want_virial ? d_virial.as<double>() : nullptr,
               (T)kHartree2KcalMol, cap1, capA1, L1.bytes, rs);
           c->launches++;
@@ -682,12 +705,12 @@ struct Engine : EngineBase {
         if (two_pass) {
           ANIB_CUDA_OK(cudaFuncSetAttribute(kern_strided, cudaFuncAttributeMaxDynamicSharedMemorySize, smem2));
           kern_strided<<<std::min(grid, 592), kAev2Warps * 32, smem2, st>>>(
-              P, c->use_cuaev ? 1 : 0, d_x4.as<V4>(), d_beg.as<int64_t>(), d_cnt.as<int>(), d_jlist.as<int>(), d_order.as<int>(),
+              P, c->use_cuaev ? 1 : 0, d_x4.as<V4>(), d_beg.as<int64_t>(), d_cnt.as<int>(), jl(), d_order.as<int>(),
               nlocal, d_daev.as<T>(), ld_aev, d_force.as<T>(), want_virial ? d_virial.as<double>() : nullptr,
               (T)kHartree2KcalMol, cap, capA, L2.bytes, rs);
         } else
           kern<<<grid, kAev2Warps * 32, smem2, st>>>(
-              P, c->use_cuaev ? 1 : 0, d_x4.as<V4>(), d_beg.as<int64_t>(), d_cnt.as<int>(), d_jlist.as<int>(), d_order.as<int>(),
+              P, c->use_cuaev ? 1 : 0, d_x4.as<V4>(), d_beg.as<int64_t>(), d_cnt.as<int>(), jl(), d_order.as<int>(),
               nlocal, d_daev.as<T>(), ld_aev, d_force.as<T>(), want_virial ? d_virial.as<double>() : nullptr,
               (T)kHartree2KcalMol, cap, capA, L2.bytes, rs);
         c->launches++;
@@ -1260,6 +1283,72 @@ int ani_debug_tc_gemm(int device, int R, int N, int K, const float* A, const flo
     return 1;
   ANIB_CUDA_OK(cudaDeviceSynchronize());
   ANIB_CUDA_OK(cudaMemcpy(C, c_d.p, (size_t)R * N * 4, cudaMemcpyDeviceToHost));
+  return 0;
+}
+
+// ---- device-resident time integration (md.cuh)
+int ani_md_nve_initial(ani_ctx* c, double* x_dev, double* v_dev, const double* f_dev, const double* mass_dev, int n, double dtv,
+                       double dtf) {
+  if (!c || (n > 0 && (!x_dev || !v_dev || !f_dev || !mass_dev))) { set_error("ani_md_nve_initial: null argument"); return 1; }
+  if (n <= 0) return 0;
+  ANIB_CUDA_OK(cudaSetDevice(c->device));
+  md_nve_initial_kernel<<<(n + 255) / 256, 256, 0, c->stream>>>(x_dev, v_dev, f_dev, mass_dev, n, dtv, dtf);
+  ANIB_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+int ani_md_nve_final(ani_ctx* c, double* v_dev, const double* f_dev, const double* mass_dev, int n, double dtf) {
+  if (!c || (n > 0 && (!v_dev || !f_dev || !mass_dev))) { set_error("ani_md_nve_final: null argument"); return 1; }
+  if (n <= 0) return 0;
+  ANIB_CUDA_OK(cudaSetDevice(c->device));
+  md_nve_final_kernel<<<(n + 255) / 256, 256, 0, c->stream>>>(v_dev, f_dev, mass_dev, n, dtf);
+  ANIB_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+int ani_md_langevin(ani_ctx* c, const double* v_dev, double* f_dev, const double* mass_dev, const int64_t* tag_dev, int n, double g1,
+                    double g2, uint64_t seed, int64_t step) {
+  if (!c || (n > 0 && (!v_dev || !f_dev || !mass_dev))) { set_error("ani_md_langevin: null argument"); return 1; }
+  if (n <= 0) return 0;
+  ANIB_CUDA_OK(cudaSetDevice(c->device));
+  md_langevin_kernel<<<(n + 255) / 256, 256, 0, c->stream>>>(v_dev, f_dev, mass_dev, (const long long*)tag_dev, n, g1, g2,
+                                                           (unsigned long long)seed, (unsigned long long)step);
+  ANIB_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+int ani_md_sum_mv2(ani_ctx* c, const double* v_dev, const double* mass_dev, int n, double* out_host) {
+  if (!c || !out_host || (n > 0 && (!v_dev || !mass_dev))) { set_error("ani_md_sum_mv2: null argument"); return 1; }
+  *out_host = 0.0;
+  if (n <= 0) return 0;
+  ANIB_CUDA_OK(cudaSetDevice(c->device));
+  const int nb = std::min(1024, (n + 255) / 256);
+  double* part = nullptr;
+  ANIB_CUDA_OK(cudaMallocAsync((void**)&part, (size_t)nb * sizeof(double), c->stream));
+  md_mv2_kernel<<<nb, 256, 0, c->stream>>>(v_dev, mass_dev, n, part);
+  std::vector<double> h(nb);
+  ANIB_CUDA_OK(cudaMemcpyAsync(h.data(), part, (size_t)nb * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  ANIB_CUDA_OK(cudaFreeAsync(part, c->stream));
+  ANIB_CUDA_OK(cudaStreamSynchronize(c->stream));
+  for (double q : h) *out_host += q;
+  return 0;
+}
+
+int ani_md_ghost_x(ani_ctx* c, double* x_dev, const int* owner_dev, const double* shift_dev, int nlocal, int nghost) {
+  if (!c || (nghost > 0 && (!x_dev || !owner_dev || !shift_dev))) { set_error("ani_md_ghost_x: null argument"); return 1; }
+  if (nghost <= 0) return 0;
+  ANIB_CUDA_OK(cudaSetDevice(c->device));
+  md_ghost_x_kernel<<<(unsigned)(((int64_t)nghost * 3 + 255) / 256), 256, 0, c->stream>>>(x_dev, owner_dev, shift_dev, nlocal, nghost);
+  ANIB_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+int ani_md_fold_ghost_f(ani_ctx* c, double* f_dev, const int* owner_dev, int nlocal, int nghost) {
+  if (!c || (nghost > 0 && (!f_dev || !owner_dev))) { set_error("ani_md_fold_ghost_f: null argument"); return 1; }
+  if (nghost <= 0) return 0;
+  ANIB_CUDA_OK(cudaSetDevice(c->device));
+  md_fold_ghost_kernel<<<(unsigned)(((int64_t)nghost * 3 + 255) / 256), 256, 0, c->stream>>>(f_dev, owner_dev, nlocal, nghost);
+  ANIB_CUDA_OK(cudaGetLastError());
   return 0;
 }
 

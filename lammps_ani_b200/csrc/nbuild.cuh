@@ -9,10 +9,20 @@
 // on beyond fp32 summation order.
 #pragma once
 #include <cub/cub.cuh>
+#include <thrust/iterator/transform_iterator.h>
 
 #include "common.cuh"
 
 namespace anib {
+
+struct NbToI64 {
+  __host__ __device__ __forceinline__ int64_t operator()(const int& v) const { return (int64_t)v; }
+};
+
+// total number of stored pairs from the exclusive scan (a one-thread kernel instead of a host pass over nlocal counts)
+__global__ void nb_total_kernel(const int64_t* __restrict__ beg, const int* __restrict__ cnt, int n, int64_t* __restrict__ out) {
+  *out = n > 0 ? beg[n - 1] + (int64_t)cnt[n - 1] : 0;
+}
 
 struct NbGrid {
   double lo[3], inv_cell;

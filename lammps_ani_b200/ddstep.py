@@ -38,6 +38,12 @@ class DomainStep:
         self.recv_back = torch.empty((self.nsend, 3), dtype=dtype, device=device)
         self.send_rows = list(halo.send_splits)
         self.recv_rows = list(halo.recv_splits)
+        # every ghost's owner INSIDE this subdomain's own replica and its displacement from it: what a single periodic domain
+        # (N = 1) would use -- identical replicas make that the exact answer of the N-rank exchange (bench.py's force check)
+        nl = self.nlocal
+        own = np.asarray(sub.ghost_owner_index, dtype=np.int64)
+        self.ghost_owner = torch.tensor(own, dtype=torch.int32, device=device)
+        self.ghost_shift = torch.tensor(sub.x[nl:] - sub.x[own], dtype=dtype, device=device).contiguous()
 
     # -- overridable primitives (GPU subclass swaps in the library kernels)
     def pack_x(self, out: torch.Tensor):
@@ -66,6 +72,20 @@ class DomainStep:
                                input_split_sizes=self.recv_rows, group=self.group)
         self.unpack_add_f(self.recv_back)
 
+    def forward_halo_local(self):
+        self.x[self.nlocal:] = self.x[self.ghost_owner.long()] + self.ghost_shift
+
+    def reverse_halo_local(self):
+        self.f.index_add_(0, self.ghost_owner.long(), self.f[self.nlocal:].clone())
+
+    def step_local_periodic(self, compute: Callable[["DomainStep"], Optional[float]]):
+        """The same step with the ghosts served from this rank's own atoms (no communication): the N = 1 periodic result."""
+        self.forward_halo_local()
+        self.f.zero_()
+        e = compute(self)
+        self.reverse_halo_local()
+        return e
+
     def step(self, compute: Callable[["DomainStep"], Optional[float]]):
         """compute(self) must ADD the forces on local+ghost atoms into self.f and may return the local energy."""
         self.forward_halo()
@@ -92,6 +112,19 @@ class GpuDomainStep(DomainStep):
     def unpack_add_f(self, buf):
         assert buf.is_contiguous()
         self.ani.halo_unpack_add_f(self.f.data_ptr(), False, self.send_index.data_ptr(), buf.data_ptr(), self.nsend)
+
+    def forward_halo_local(self):
+        _md = self.ani._L.ani_md_ghost_x
+        from .runner import _check
+        import ctypes as C
+        _check(_md(self.ani._ctx, C.c_void_p(self.x.data_ptr()), C.c_void_p(self.ghost_owner.data_ptr()),
+                   C.c_void_p(self.ghost_shift.data_ptr()), self.nlocal, self.ntotal - self.nlocal))
+
+    def reverse_halo_local(self):
+        from .runner import _check
+        import ctypes as C
+        _check(self.ani._L.ani_md_fold_ghost_f(self.ani._ctx, C.c_void_p(self.f.data_ptr()), C.c_void_p(self.ghost_owner.data_ptr()),
+                                              self.nlocal, self.ntotal - self.nlocal))
 
     def pair_compute(self, want_energy: bool = False):
         e, _ = self.ani.compute_device(self.x.data_ptr(), False, self.f.data_ptr(), False, 0, want_energy=want_energy)

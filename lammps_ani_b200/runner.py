@@ -62,13 +62,20 @@ def load_library():
     L.ani_debug_get_aev.argtypes = [vp, vp, vp]
     L.ani_debug_tc_gemm.argtypes = [i32, i32, i32, i32, vp, vp, vp, i32]
     L.ani_debug_tc_gemm.restype = i32
+    L.ani_md_nve_initial.argtypes = [vp, vp, vp, vp, vp, i32, C.c_double, C.c_double]
+    L.ani_md_nve_final.argtypes = [vp, vp, vp, vp, i32, C.c_double]
+    L.ani_md_langevin.argtypes = [vp, vp, vp, vp, vp, i32, C.c_double, C.c_double, C.c_uint64, i64]
+    L.ani_md_sum_mv2.argtypes = [vp, vp, vp, i32, dp]
+    L.ani_md_ghost_x.argtypes = [vp, vp, vp, vp, i32, i32]
+    L.ani_md_fold_ghost_f.argtypes = [vp, vp, vp, i32, i32]
     L.ani_halo_pack_x.argtypes = [vp, vp, i32, vp, vp, i64, vp]
     L.ani_halo_unpack_add_f.argtypes = [vp, vp, i32, vp, vp, i64]
     for name in ("ani_model_load", "ani_model_info", "ani_ctx_create", "ani_ctx_set_mlp_mode", "ani_ctx_set_option", "ani_ctx_set_stream",
                  "ani_ctx_reset_stream", "ani_ctx_synchronize", "ani_ctx_enable_timing", "ani_last_timing", "ani_set_neighbors_full",
                  "ani_set_neighbors_half", "ani_set_neighbors_table", "ani_device_count", "ani_compute",
                  "ani_compute_device", "ani_debug_get_aev", "ani_halo_pack_x", "ani_halo_unpack_add_f", "ani_build_neighbors",
-                 "ani_debug_get_neighbors"):
+                 "ani_debug_get_neighbors", "ani_md_nve_initial", "ani_md_nve_final", "ani_md_langevin", "ani_md_sum_mv2",
+                 "ani_md_ghost_x", "ani_md_fold_ghost_f"):
         getattr(L, name).restype = i32
     _lib = L
     return L
@@ -80,6 +87,7 @@ EXPORTED_SYMBOLS = [
     "ani_compute_device", "ani_halo_pack_x", "ani_halo_unpack_add_f", "ani_debug_get_aev", "ani_last_timing",
     "ani_ctx_enable_timing", "ani_last_error", "ani_abi_version", "ani_debug_tc_gemm", "ani_set_neighbors_table",
     "ani_device_count", "ani_build_neighbors", "ani_debug_get_neighbors", "ani_ctx_release_host_buffers", "ani_ctx_set_option",
+    "ani_md_nve_initial", "ani_md_nve_final", "ani_md_langevin", "ani_md_sum_mv2", "ani_md_ghost_x", "ani_md_fold_ghost_f",
 ]
 
 
@@ -267,6 +275,23 @@ class ANI:
                                           int(f_is_float), C.c_void_p(eatom_ptr or 0),
                                           C.addressof(energy) if want_energy else None, _ptr(virial)))
         return (energy.value if want_energy else None), (virial.reshape(3, 3) if want_virial else None)
+
+    # ---- device-resident integration (fix nve / fix langevin on the GPU; include/ani_b200.h ani_md_*): raw device pointers
+    def md_nve_initial(self, x_ptr, v_ptr, f_ptr, mass_ptr, n, dtv, dtf):
+        _check(self._L.ani_md_nve_initial(self._ctx, C.c_void_p(x_ptr), C.c_void_p(v_ptr), C.c_void_p(f_ptr), C.c_void_p(mass_ptr),
+                                          int(n), float(dtv), float(dtf)))
+
+    def md_nve_final(self, v_ptr, f_ptr, mass_ptr, n, dtf):
+        _check(self._L.ani_md_nve_final(self._ctx, C.c_void_p(v_ptr), C.c_void_p(f_ptr), C.c_void_p(mass_ptr), int(n), float(dtf)))
+
+    def md_langevin(self, v_ptr, f_ptr, mass_ptr, tag_ptr, n, g1, g2, seed, step):
+        _check(self._L.ani_md_langevin(self._ctx, C.c_void_p(v_ptr), C.c_void_p(f_ptr), C.c_void_p(mass_ptr), C.c_void_p(tag_ptr or 0),
+                                       int(n), float(g1), float(g2), int(seed), int(step)))
+
+    def md_sum_mv2(self, v_ptr, mass_ptr, n) -> float:
+        out = C.c_double()
+        _check(self._L.ani_md_sum_mv2(self._ctx, C.c_void_p(v_ptr), C.c_void_p(mass_ptr), int(n), C.byref(out)))
+        return out.value
 
     def halo_pack_x(self, x_ptr, is_float, index_ptr, shift_ptr, n, out_ptr):
         _check(self._L.ani_halo_pack_x(self._ctx, C.c_void_p(x_ptr), int(is_float), C.c_void_p(index_ptr),
