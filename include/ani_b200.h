@@ -13,6 +13,7 @@
 #ifndef ANI_B200_H
 #define ANI_B200_H
 
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
@@ -153,6 +154,15 @@ int ani_md_langevin(ani_ctx* ctx, const double* v_dev, double* f_dev, const doub
 int ani_md_sum_mv2(ani_ctx* ctx, const double* v_dev, const double* mass_dev, int n, double* out_host);
 int ani_md_ghost_x(ani_ctx* ctx, double* x_dev, const int* owner_dev, const double* shift_dev, int nlocal, int nghost);
 int ani_md_fold_ghost_f(ani_ctx* ctx, double* f_dev, const int* owner_dev, int nlocal, int nghost);
+
+/* Device-memory helpers on the context's device and stream, for callers that do not link the CUDA runtime (the LAMMPS
+ * plugin's device-resident mode): alloc / free, blocking upload / download ordered after everything queued on the context's
+ * stream (download also reports pending device-side error flags), asynchronous zero fill. */
+int ani_dev_alloc(ani_ctx* ctx, size_t bytes, void** out_dev);
+int ani_dev_free(ani_ctx* ctx, void* dev);
+int ani_dev_upload(ani_ctx* ctx, void* dst_dev, const void* src_host, size_t bytes);
+int ani_dev_download(ani_ctx* ctx, void* dst_host, const void* src_dev, size_t bytes);
+int ani_dev_zero(ani_ctx* ctx, void* dst_dev, size_t bytes);
 
 /* ---- introspection for tests, profiling and bench ------------------------------------------------------- */
 /* Copy the AEV rows / dE/dAEV rows of the local atoms (atom order, [nlocal][aev_length] doubles) of the

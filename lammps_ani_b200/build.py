@@ -38,12 +38,12 @@ PLUGIN = os.path.join(HERE, "ani_plugin.so")
 def build_plugin(force: bool = False) -> str:
     """C++ LAMMPS plugin (pair styles `ani`, `ani/kk`) against the LAMMPS headers; links only libani_b200."""
     src_dir = os.path.join(HERE, "lammps")
-    srcs = [os.path.join(src_dir, f) for f in ("pair_ani.cpp", "ani_plugin.cpp")]
+    srcs = [os.path.join(src_dir, f) for f in ("pair_ani.cpp", "fix_ani_md.cpp", "ani_plugin.cpp")]
     if not all(os.path.exists(s) for s in srcs):
         raise RuntimeError("plugin sources not present yet")
     if not os.path.exists(os.path.join(LAMMPS_SRC, "pair.h")):
         raise RuntimeError(f"LAMMPS headers not found under {LAMMPS_SRC}")
-    if not force and os.path.exists(PLUGIN) and all(os.path.getmtime(s) < os.path.getmtime(PLUGIN) for s in srcs):
+    if not force and os.path.exists(PLUGIN) and all(os.path.getmtime(s) < os.path.getmtime(PLUGIN) for s in srcs + [os.path.join(src_dir, h) for h in ("pair_ani.h", "fix_ani_md.h")]):
         return PLUGIN
     cmd = ["/usr/bin/g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-DLAMMPS_SMALLBIG", f"-I{LAMMPS_SRC}",
            f"-I{LAMMPS_SRC}/STUBS", f"-I{os.path.join(HERE, '..', 'include')}"] + srcs + \

@@ -1286,6 +1286,44 @@ int ani_debug_tc_gemm(int device, int R, int N, int K, const float* A, const flo
   return 0;
 }
 
+// ---- plain device-memory helpers for callers that do not link the CUDA runtime themselves (the LAMMPS plugin)
+int ani_dev_alloc(ani_ctx* c, size_t bytes, void** out) {
+  if (!c || !out) { set_error("ani_dev_alloc: null argument"); return 1; }
+  ANIB_CUDA_OK(cudaSetDevice(c->device));
+  *out = nullptr;
+  ANIB_CUDA_OK(cudaMalloc(out, std::max<size_t>(bytes, 16)));
+  return 0;
+}
+int ani_dev_free(ani_ctx* c, void* p) {
+  if (!c) { set_error("ani_dev_free: null context"); return 1; }
+  ANIB_CUDA_OK(cudaSetDevice(c->device));
+  if (p) { ANIB_CUDA_OK(cudaStreamSynchronize(c->stream)); ANIB_CUDA_OK(cudaFree(p)); }
+  return 0;
+}
+int ani_dev_upload(ani_ctx* c, void* dst_dev, const void* src_host, size_t bytes) {      // ordered on the context's stream, returns when done
+  if (!c || (bytes && (!dst_dev || !src_host))) { set_error("ani_dev_upload: null argument"); return 1; }
+  if (!bytes) return 0;
+  ANIB_CUDA_OK(cudaSetDevice(c->device));
+  ANIB_CUDA_OK(cudaMemcpyAsync(dst_dev, src_host, bytes, cudaMemcpyHostToDevice, c->stream));
+  ANIB_CUDA_OK(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+int ani_dev_download(ani_ctx* c, void* dst_host, const void* src_dev, size_t bytes) {
+  if (!c || (bytes && (!dst_host || !src_dev))) { set_error("ani_dev_download: null argument"); return 1; }
+  if (!bytes) return 0;
+  ANIB_CUDA_OK(cudaSetDevice(c->device));
+  ANIB_CUDA_OK(cudaMemcpyAsync(dst_host, src_dev, bytes, cudaMemcpyDeviceToHost, c->stream));
+  ANIB_CUDA_OK(cudaStreamSynchronize(c->stream));
+  return c->eng ? c->eng->check_errors() : 0;
+}
+int ani_dev_zero(ani_ctx* c, void* dst_dev, size_t bytes) {
+  if (!c || (bytes && !dst_dev)) { set_error("ani_dev_zero: null argument"); return 1; }
+  if (!bytes) return 0;
+  ANIB_CUDA_OK(cudaSetDevice(c->device));
+  ANIB_CUDA_OK(cudaMemsetAsync(dst_dev, 0, bytes, c->stream));
+  return 0;
+}
+
 // ---- device-resident time integration (md.cuh)
 int ani_md_nve_initial(ani_ctx* c, double* x_dev, double* v_dev, const double* f_dev, const double* mass_dev, int n, double dtv,
                        double dtf) {

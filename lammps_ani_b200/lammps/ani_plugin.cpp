@@ -4,12 +4,14 @@
 #include "lammpsplugin.h"
 #include "version.h"
 
+#include "fix_ani_md.h"
 #include "pair_ani.h"
 
 using namespace LAMMPS_NS;
 
 static Pair* make_ani(LAMMPS* lmp) { return new PairANIB200(lmp); }
 static Pair* make_ani_device(LAMMPS* lmp) { return new PairANIB200Device(lmp); }
+static Fix* make_ani_md(LAMMPS* lmp, int narg, char** arg) { return new FixANIMD(lmp, narg, arg); }
 
 extern "C" void lammpsplugin_init(void* lmp, void* handle, void* regfunc) {
   lammpsplugin_regfunc reg = (lammpsplugin_regfunc)regfunc;
@@ -27,5 +29,12 @@ extern "C" void lammpsplugin_init(void* lmp, void* handle, void* regfunc) {
   p.name = "ani/kk";
   p.info = "ANI pair style, device-resident variant (libani_b200)";
   p.creator.v1 = (lammpsplugin_factory1*)&make_ani_device;
+  (*reg)(&p, lmp);
+
+  // not in the reference: the device-resident integrator / thermostat next to `ani_neighbor device`
+  p.style = "fix";
+  p.name = "ani/md";
+  p.info = "velocity Verlet + Langevin thermostat on the GPU for pair_style ani (libani_b200)";
+  p.creator.v2 = (lammpsplugin_factory2*)&make_ani_md;
   (*reg)(&p, lmp);
 }

@@ -9,6 +9,7 @@
  */
 #include "pair_ani.h"
 
+#include <algorithm>
 #include <cstdlib>
 #include <cstring>
 
@@ -57,6 +58,7 @@ void PairANIB200::fail(const char* what) {
 }
 
 void PairANIB200::close_model() {
+  resident_free();
   if (ctx) ani_ctx_destroy(ctx);
   if (model) ani_model_free(model);
   ctx = nullptr;
@@ -172,8 +174,103 @@ double PairANIB200::memory_usage() {
                   atom_index12.capacity() * sizeof(int64_t) + (out_force.capacity() + out_eatom.capacity()) * sizeof(double));
 }
 
+/* ------------------------------------------------------------------------------------------------ device-resident mode */
+void PairANIB200::resident_free() {
+  if (!ctx) return;
+  ani_dev_free(ctx, res.x); ani_dev_free(ctx, res.f); ani_dev_free(ctx, res.shift); ani_dev_free(ctx, res.owner);
+  res = Resident();
+}
+
+void PairANIB200::set_resident(bool on) {
+  if (on && !device_list) error->all(FLERR, "fix ani/md needs pair_style ani ... with ani_neighbor device");
+  if (on && (force->newton || comm->nprocs > 1))
+    error->all(FLERR, "fix ani/md: the device-resident mode covers one rank with newton off (ghosts are periodic images of local atoms)");
+  res.on = on;
+  res.valid = false;
+}
+
+void PairANIB200::download_x() {
+  if (res.valid && atom->nlocal > 0 && ani_dev_download(ctx, &atom->x[0][0], res.x, (size_t)atom->nlocal * 3 * sizeof(double)))
+    fail("download of the positions failed");
+}
+
+void PairANIB200::download_f() {
+  if (res.valid && atom->nlocal > 0 && ani_dev_download(ctx, &atom->f[0][0], res.f, (size_t)atom->nlocal * 3 * sizeof(double)))
+    fail("download of the forces failed");
+}
+
+/* One step with x / f on the device.  Rebuild steps (neighbor->ago == 0): LAMMPS has just re-wrapped, sorted and re-ghosted the
+ * HOST arrays, so positions (local + ghost) go up once, each ghost's owner and displacement are recorded (every ghost of a
+ * single periodic rank is an image of a local atom: atom->map(tag)), and the list is built on the device.  Other steps: the
+ * local positions on the device were advanced by fix ani/md; ghosts = owner + shift (CommBrick::forward_comm's job).  Forces
+ * are accumulated into the device array and the ghost part is folded onto the owners there (pair_ani.cpp:197-201). */
+void PairANIB200::resident_compute(int eflag, int vflag) {
+  const int nlocal = atom->nlocal, nghost = atom->nghost, ntotal = nlocal + nghost;
+  double** x = atom->x;
+  if (neighbor->ago == 0 || !res.valid) {
+    if (ntotal > res.cap_total || nghost > res.cap_ghost) {
+      ani_dev_free(ctx, res.x); ani_dev_free(ctx, res.f); ani_dev_free(ctx, res.shift); ani_dev_free(ctx, res.owner);
+      res.cap_total = ntotal + ntotal / 8 + 64; res.cap_ghost = nghost + nghost / 8 + 64;
+      if (ani_dev_alloc(ctx, (size_t)res.cap_total * 3 * sizeof(double), (void**)&res.x) ||
+          ani_dev_alloc(ctx, (size_t)res.cap_total * 3 * sizeof(double), (void**)&res.f) ||
+          ani_dev_alloc(ctx, (size_t)res.cap_ghost * 3 * sizeof(double), (void**)&res.shift) ||
+          ani_dev_alloc(ctx, (size_t)res.cap_ghost * sizeof(int), (void**)&res.owner))
+        fail("device allocation failed");
+    }
+    const int* type = atom->type;
+    const tagint* tag = atom->tag;
+    if ((size_t)ntotal > species.size()) species.resize((size_t)ntotal + ntotal / 2);
+    for (int i = 0; i < ntotal; i++) species[i] = type[i] - 1;
+    h_owner.resize((size_t)std::max(nghost, 1));
+    h_shift.resize((size_t)std::max(nghost, 1) * 3);
+    // every ghost of a single periodic rank is an image of a local atom: tag -> local index (no atom map needed)
+    tagint maxtag = 0;
+    for (int i = 0; i < nlocal; i++) maxtag = std::max(maxtag, tag[i]);
+    h_tag2local.assign((size_t)maxtag + 1, -1);
+    for (int i = 0; i < nlocal; i++) h_tag2local[tag[i]] = i;
+    for (int g = 0; g < nghost; g++) {
+      const tagint tg = tag[nlocal + g];
+      const int o = (tg >= 0 && tg <= maxtag) ? h_tag2local[tg] : -1;
+      if (o < 0) error->one(FLERR, "fix ani/md: a ghost atom has no local owner");
+      h_owner[g] = o;
+      for (int d = 0; d < 3; d++) h_shift[3 * (size_t)g + d] = x[nlocal + g][d] - x[o][d];
+    }
+    if (ani_dev_upload(ctx, res.x, ntotal > 0 ? &x[0][0] : nullptr, (size_t)ntotal * 3 * sizeof(double)) ||
+        ani_dev_upload(ctx, res.owner, h_owner.data(), (size_t)nghost * sizeof(int)) ||
+        ani_dev_upload(ctx, res.shift, h_shift.data(), (size_t)nghost * 3 * sizeof(double)))
+      fail("upload failed");
+    double lo[3], hi[3];
+    for (int d = 0; d < 3; d++) {
+      lo[d] = domain->sublo[d] - comm->cutghost[d];
+      hi[d] = domain->subhi[d] + comm->cutghost[d];
+    }
+    int64_t np = 0;
+    if (ani_build_neighbors(ctx, nlocal, ntotal, species.data(), res.x, 1, neighbor->cutneighmax, lo, hi, &np))
+      fail("device neighbour build failed");
+    npairs = np;
+    res.nlocal = nlocal; res.nghost = nghost;
+    res.valid = true;
+    res.rebuilt_step = update->ntimestep;
+  } else {
+    if (nlocal != res.nlocal || nghost != res.nghost) error->one(FLERR, "fix ani/md: atom counts changed without a neighbour rebuild");
+    if (ani_md_ghost_x(ctx, res.x, res.owner, res.shift, nlocal, nghost)) fail("ghost update failed");
+  }
+  if (ani_dev_zero(ctx, res.f, (size_t)ntotal * 3 * sizeof(double))) fail("force clear failed");
+  double energy = 0.0, vir9[9];
+  if (ani_compute_device(ctx, res.x, 0, res.f, 0, nullptr, eflag_global ? &energy : nullptr, vflag_either ? vir9 : nullptr))
+    fail("evaluation failed");
+  if (ani_md_fold_ghost_f(ctx, res.f, res.owner, nlocal, nghost)) fail("ghost force fold failed");
+  if (eflag_atom) error->one(FLERR, "fix ani/md: per-atom energies are not available in the device-resident mode");
+  if (eflag_global) eng_vdwl += energy;
+  if (vflag_either) {
+    virial[0] += vir9[0]; virial[1] += vir9[4]; virial[2] += vir9[8];
+    virial[3] += vir9[1]; virial[4] += vir9[2]; virial[5] += vir9[5];
+  }
+}
+
 void PairANIB200::compute(int eflag, int vflag) {
   ev_init(eflag, vflag);
+  if (res.on) { resident_compute(eflag, vflag); return; }
   const int nlocal = atom->nlocal;
   const int ntotal = nlocal + atom->nghost;
   double** x = atom->x;

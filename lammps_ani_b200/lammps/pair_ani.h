@@ -52,6 +52,28 @@ class PairANIB200 : public Pair {
   int64_t npairs;
   std::vector<double> out_force, out_eatom;
 
+  // ---- device-resident mode, switched on by `fix ani/md`: x, f (and the fix's v) live on the GPU between
+  // neighbour rebuilds; ghost positions are regenerated from their owners and ghost forces folded on the device; the host
+  // arrays are refreshed only when LAMMPS needs them (rebuild checks, thermo / dump steps)
+ public:
+  struct Resident {
+    bool on = false, valid = false;     // requested by a fix / device arrays hold the current state
+    double *x = nullptr, *f = nullptr, *shift = nullptr;
+    int* owner = nullptr;
+    int cap_total = 0, cap_ghost = 0, nlocal = 0, nghost = 0;
+    bigint rebuilt_step = -1;           // timestep of the last upload after a rebuild (the fix re-uploads v when it changes)
+  } res;
+  ani_ctx* context() { return ctx; }
+  void set_resident(bool on);
+  void download_x();                    // device -> atom->x (local atoms)
+  void download_f();                    // device -> atom->f (local atoms, overwrite)
+
+ protected:
+  void resident_compute(int eflag, int vflag);
+  void resident_free();
+  std::vector<int> h_owner, h_tag2local;
+  std::vector<double> h_shift;
+
   virtual void allocate();
   int local_device(const std::string& device);
   void open_model();

@@ -88,6 +88,7 @@ EXPORTED_SYMBOLS = [
     "ani_ctx_enable_timing", "ani_last_error", "ani_abi_version", "ani_debug_tc_gemm", "ani_set_neighbors_table",
     "ani_device_count", "ani_build_neighbors", "ani_debug_get_neighbors", "ani_ctx_release_host_buffers", "ani_ctx_set_option",
     "ani_md_nve_initial", "ani_md_nve_final", "ani_md_langevin", "ani_md_sum_mv2", "ani_md_ghost_x", "ani_md_fold_ghost_f",
+    "ani_dev_alloc", "ani_dev_free", "ani_dev_upload", "ani_dev_download", "ani_dev_zero",
 ]
 
 

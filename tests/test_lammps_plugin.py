@@ -173,3 +173,45 @@ def test_restart_round_trip(tmp_path, ani1xnr_path, nbr, prec):
     orc = OracleANI(ani1xnr_path)
     lo, hi = _box_of("water30.data")
     check_frame_against_oracle(orc, frames[3], th[3], lo, hi, prec == "single")
+
+
+@pytest.mark.gpu
+@needs_lmp
+@pytest.mark.parametrize("prec", ["double", "single"])
+def test_device_resident_integrator_matches_fix_nve(tmp_path, ani1xnr_path, prec):
+    """`fix ani/md` (velocity Verlet on the GPU, x / v / f resident between rebuilds) against LAMMPS's own
+    `fix nve` on the same input: 20 steps of 0.1 fs with a rebuild every 2 steps (so the upload-after-rebuild path runs ten
+    times), forces / positions dumped every step, thermo (pe, ke from the downloaded v, pair pressure) every step."""
+    base = (("ani_neighbor", "device"), ("ani_precision", prec), ("steps", 20))
+    d0, d1 = tmp_path / "nve", tmp_path / "md"
+    d0.mkdir(); d1.mkdir()
+    r0 = run_lmp(d0, ani1xnr_path, *base, ("integrator", "nve"))
+    r1 = run_lmp(d1, ani1xnr_path, *base, ("integrator", "ani/md"))
+    assert r0.returncode == 0, r0.stdout[-2000:] + r0.stderr[-2000:]
+    assert r1.returncode == 0, r1.stdout[-2000:] + r1.stderr[-2000:]
+    t0, t1 = _thermo(r0.stdout), _thermo(r1.stdout)
+    f0, f1 = _dump_forces(os.path.join(d0, "dump.forces")), _dump_forces(os.path.join(d1, "dump.forces"))
+    assert t0.shape == t1.shape == (21, 10) and len(f0) == len(f1) == 21
+    xtol, ftol, etol = (1e-10, 1e-8, 1e-11) if prec == "double" else (2e-6, 2e-4 * EV2KCAL, 2e-7)
+    for k in range(21):
+        assert np.abs(f0[k][:, 2:5] - f1[k][:, 2:5]).max() <= xtol, f"positions differ at step {k}"
+        assert np.abs(f0[k][:, 5:8] - f1[k][:, 5:8]).max() <= ftol, f"forces differ at step {k}"
+        assert abs(t0[k, 1] - t1[k, 1]) <= etol * abs(t0[k, 1]) and abs(t0[k, 2] - t1[k, 2]) <= 1e-6 * max(1.0, abs(t0[k, 2]))
+    # NVE through LAMMPS: the conserved quantity of the device-resident run
+    assert abs(t1[20, 3] - t1[0, 3]) < 2e-2
+    orc = OracleANI(ani1xnr_path)
+    lo, hi = _box_of("water30.data")
+    check_frame_against_oracle(orc, f1[20], t1[20], lo, hi, prec == "single")
+
+
+@pytest.mark.gpu
+@needs_lmp
+def test_device_resident_langevin_thermostat(tmp_path, ani1xnr_path):
+    """fix ani/md langevin: the thermostat pulls a cold start towards the target temperature (uniform-noise Langevin as
+    fix_langevin.cpp; the random stream is a counter-based hash, so only statistics can be compared with LAMMPS's)."""
+    r = run_lmp(tmp_path, ani1xnr_path, ("ani_neighbor", "device"), ("ani_precision", "single"), ("steps", 400),
+                ("integrator", "ani/md langevin 300.0 300.0 20.0 4711"), script="in.langevin")
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    rows = [[float(v) for v in l.split()] for l in r.stdout.splitlines() if len(l.split()) == 3 and l.split()[0].isdigit()]
+    T = np.array([row[1] for row in rows])
+    assert T[0] < 1e-6 and 120.0 < T[-5:].mean() < 600.0, T      # 30 atoms: large fluctuations around 300 K

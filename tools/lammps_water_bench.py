@@ -5,7 +5,13 @@ yes, velocity 300 K, fix langevin + fix nve, dt 0.5 fs) run by a STOCK serial LA
 Kokkos -- so the "Loop time" of this run is an upper bound on what the plain `ani` style costs end to end, and its Pair line
 is the pair style's own cost (host flatten of the list on rebuild steps, H2D/D2H, kernels).
 
-usage: python tools/lammps_water_bench.py [--cells 19 19 19] [--steps 200] [--model lammps_ani_b200/data/ani1x_nr.aniw]
+`--integrator device` replaces `fix langevin` + `fix nve` by `fix ani/md langevin ...`: integration and thermostat
+run on the GPU next to `ani_neighbor device`, x / v / f stay there between rebuilds.
+
+The model defaults to the ANI-2x-shape synthetic ensemble (what the water configs of BASELINE.json are quoted on; seeded random
+weights, so the trajectory is not physical); `--model` takes any .aniw, e.g. the real ANI-1xnr weights.
+
+usage: python tools/lammps_water_bench.py [--cells 19 19 19] [--steps 200] [--neighbor device] [--integrator device] [--model x.aniw]
 """
 import argparse
 import os
@@ -32,8 +38,7 @@ plugin         load {plugin}
 pair_style     ani 5.1 {model} cuda -1 cuaev {nbr} single
 pair_coeff     * *
 velocity       all create 300.0 12345 rot yes mom yes dist gaussian
-fix            1 all langevin 300.0 300.0 100.0 12345
-fix            2 all nve
+{fixes}
 timestep       0.5
 thermo         {thermo}
 run            {warm}
@@ -47,8 +52,19 @@ def main():
     ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warm", type=int, default=50)
     ap.add_argument("--neighbor", default="full", help="full | half | device (list built on the GPU by the library)")
-    ap.add_argument("--model", default=os.path.join(ROOT, "lammps_ani_b200", "data", "ani1x_nr.aniw"))
+    ap.add_argument("--integrator", default="lammps", help="lammps (fix langevin + fix nve on the host) | device (fix ani/md langevin)")
+    ap.add_argument("--model", default="")
     args = ap.parse_args()
+    if not args.model:
+        import bench
+        args.model = bench.model_path()
+    label = "ANI-2x shapes, seeded random weights" if "synthetic" in os.path.basename(args.model) else os.path.basename(args.model)
+    if args.integrator == "device":
+        fixes = "fix            1 all ani/md langevin 300.0 300.0 100.0 12345"
+        if args.neighbor != "device":
+            ap.error("--integrator device needs --neighbor device")
+    else:
+        fixes = "fix            1 all langevin 300.0 300.0 100.0 12345\nfix            2 all nve"
     lmp = os.path.join(ROOT, "tools", "_lmp", "lmp")
     plugin = os.path.join(ROOT, "lammps_ani_b200", "ani_plugin.so")
     x, sp, box = domain.make_water_box(tuple(args.cells), seed=12345, jitter=0.1)
@@ -63,7 +79,7 @@ def main():
                 f.write(f"{i + 1} {int(sp[i]) + 1} {x[i, 0]:.10f} {x[i, 1]:.10f} {x[i, 2]:.10f}\n")
         inp = os.path.join(tmp, "in.bench")
         open(inp, "w").write(IN.format(data=data, plugin=plugin, model=args.model, thermo=max(args.steps // 4, 1), warm=args.warm, nbr=args.neighbor,
-                                       steps=args.steps))
+                                       steps=args.steps, fixes=fixes))
         env = dict(os.environ, LD_LIBRARY_PATH=os.path.dirname(plugin) + ":" + os.environ.get("LD_LIBRARY_PATH", ""))
         r = subprocess.run([lmp, "-in", inp, "-log", "none"], cwd=tmp, env=env, capture_output=True, text=True)
         out = r.stdout
@@ -75,7 +91,8 @@ def main():
         loops = [ln for ln in out.splitlines() if ln.startswith("Loop time")]
         if loops:
             t = float(loops[-1].split()[3]); n = int(loops[-1].split()[-2]); st = int(loops[-1].split()[8])
-            print(f"==> {n} atoms, {st} steps, {t:.3f} s: {n * st / t / 1e6:.3f} M atom-timesteps/s through stock serial LAMMPS (plain `ani` style, ani_neighbor {args.neighbor})")
+            print(f"==> {n} atoms, {st} steps, {t:.3f} s: {n * st / t / 1e6:.3f} M atom-timesteps/s through stock serial LAMMPS (plain `ani` style, model: {label}, "
+                  f"ani_neighbor {args.neighbor}, integrator {args.integrator})")
         return r.returncode
 
 
