@@ -51,6 +51,11 @@ def parse_args():
     ap.add_argument("--cpu-sample-atoms", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true", default=bool(os.environ.get("ANI_BENCH_NO_CPU")))
     ap.add_argument("--no-md", action="store_true", help="skip the MD leg (value_md)")
+    ap.add_argument("--workload", default="water", choices=["water", "combustion"],
+                    help="water: BASELINE.json configs 2/4 (ANI-2x shapes); combustion: config 5 (CH4 + 2 O2 at 0.25 g/cc, ANI-1xnr "
+                         "weights + RepulsionXTB, half neighbour list)")
+    ap.add_argument("--nbr", default="", choices=["", "full", "half"], help="neighbour list kind (default: full for water, half for combustion)")
+    ap.add_argument("--no-repulsion", action="store_true", help="combustion workload without the RepulsionXTB term")
     return ap.parse_args()
 
 
@@ -66,10 +71,33 @@ def model_path(num_models_total=8):
     return p
 
 
-def build_system(atoms_per_gpu, grid, rank):
+def combustion_model_path(repulsion=True):
+    """The in-tree ANI-1xnr ensemble (real trained weights), optionally with the RepulsionXTB tables switched on (the
+    `ani1x_nr_repulsion.pt` of examples/combustion/README.md)."""
+    from lammps_ani_b200 import aniw, extract
+    d = os.path.join(ROOT, "lammps_ani_b200", "data")
+    base = os.path.join(d, "ani1x_nr.aniw")
+    if not os.path.exists(base):
+        raise RuntimeError(f"{base} is missing (python __graft_entry__.py extracts it where /root/reference exists)")
+    if not repulsion:
+        return base
+    p = os.path.join(d, "ani1x_nr_repulsion.aniw")
+    if not os.path.exists(p):
+        tmp = p + f".tmp{os.getpid()}"
+        aniw.save(extract.with_repulsion(aniw.load(base)), tmp)
+        os.replace(tmp, p)
+    return p
+
+
+def build_system(atoms_per_gpu, grid, rank, workload="water"):
     from lammps_ani_b200 import domain
-    cells = domain.cells_for_atoms(atoms_per_gpu)
-    x, sp, box = domain.make_water_box(cells, seed=12345)
+    if workload == "combustion":
+        n = max(1, atoms_per_gpu // 9)
+        x, sp, box = domain.make_combustion_box(n, seed=12345)
+        cells = (n, 2 * n, 0)
+    else:
+        cells = domain.cells_for_atoms(atoms_per_gpu)
+        x, sp, box = domain.make_water_box(cells, seed=12345)
     sub = domain.decompose(x, sp, box, (1, 1, 1))[0]
     halo = domain.replica_halo(sub, box, grid, rank)
     il, nn, jl = domain.full_neighbor_list(sub.x, sub.nlocal)
@@ -285,19 +313,26 @@ def main():
         model_path()
     if world > 1:
         dist.barrier()
-    model = model_path()
+    combustion = args.workload == "combustion"
+    nbr_kind = args.nbr or ("half" if combustion else "full")
+    if rank == 0 and combustion:
+        combustion_model_path(not args.no_repulsion)
+        if world > 1:
+            pass
+    model = combustion_model_path(not args.no_repulsion) if combustion else model_path()
     params = aniw.load(model)
     grid = domain.grid_for_ranks(world)
     t_setup = time.time()
-    cells, box, sub, halo, il, nn, jl = build_system(args.atoms, grid, rank)
+    cells, box, sub, halo, il, nn, jl = build_system(args.atoms, grid, rank, args.workload)
     M = args.models
-    ani = runner.ANI(model, local_rank, M, use_cuaev=True, use_fullnbr=True, use_single=True)
+    ani = runner.ANI(model, local_rank, M, use_cuaev=True, use_fullnbr=(nbr_kind == "full"), use_single=True)
     mode_names = {"simt": runner.MLP_FP32_SIMT, "tf32x3": runner.MLP_TF32X3, "tf32": runner.MLP_TF32, "f16x3": runner.MLP_F16X3}
     if not args.mlp_mode:
         args.mlp_mode = "f16x3"
     if args.mlp_mode:
         ani.set_mlp_mode(mode_names[args.mlp_mode])
-    step = GpuDomainStep(ani, sub, halo, dev, il, nn, jl)
+    idx12 = domain.half_neighbor_list(sub.x, sub.nlocal) if nbr_kind == "half" else None
+    step = GpuDomainStep(ani, sub, halo, dev, il, nn, jl, atom_index12=idx12)
     t_setup = time.time() - t_setup
     nlocal, ntotal = sub.nlocal, sub.ntotal
 
@@ -353,18 +388,25 @@ def main():
     ani.enable_timing(False)
     # ---------------- rebuild step (`neighbor->ago == 0`): list built on the device from the device coordinates (row f2)
     # against installing a host-built list (the reference's path: host flatten + H2D of the list, pair_ani.cpp:107-151)
+    rebuild_dev_ms = rebuild_host_ms = None
     lo_bb, hi_bb = sub.x.min(0) - 1e-6, sub.x.max(0) + 1e-6
-    ani.build_neighbors(sub.species, None, nlocal, domain_list_cutoff(), lo=lo_bb, hi=hi_bb, x_dev_ptr=step.x.data_ptr())   # allocations
-    torch.cuda.synchronize()
-    t0 = time.perf_counter()
-    npairs_dev = ani.build_neighbors(sub.species, None, nlocal, domain_list_cutoff(), lo=lo_bb, hi=hi_bb, x_dev_ptr=step.x.data_ptr())
-    torch.cuda.synchronize()
-    rebuild_dev_ms = (time.perf_counter() - t0) * 1e3
-    t0 = time.perf_counter()
-    ani.set_neighbors_full(sub.species, il, nn, jl, nlocal)
-    torch.cuda.synchronize()
-    rebuild_host_ms = (time.perf_counter() - t0) * 1e3
-    assert npairs_dev == int(jl.size), "device-built list differs from the host list"
+    if nbr_kind == "half":
+        t0 = time.perf_counter()
+        ani.set_neighbors_half(sub.species, idx12, nlocal)
+        torch.cuda.synchronize()
+        rebuild_host_ms = (time.perf_counter() - t0) * 1e3
+    else:
+        ani.build_neighbors(sub.species, None, nlocal, domain_list_cutoff(), lo=lo_bb, hi=hi_bb, x_dev_ptr=step.x.data_ptr())   # allocations
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        npairs_dev = ani.build_neighbors(sub.species, None, nlocal, domain_list_cutoff(), lo=lo_bb, hi=hi_bb, x_dev_ptr=step.x.data_ptr())
+        torch.cuda.synchronize()
+        rebuild_dev_ms = (time.perf_counter() - t0) * 1e3
+        t0 = time.perf_counter()
+        ani.set_neighbors_full(sub.species, il, nn, jl, nlocal)
+        torch.cuda.synchronize()
+        rebuild_host_ms = (time.perf_counter() - t0) * 1e3
+        assert npairs_dev == int(jl.size), "device-built list differs from the host list"
     # ---------------- multi-GPU force check: identical replicas make the N-rank answer equal to the single periodic domain's
     force_check = None
     if world > 1:
@@ -382,10 +424,11 @@ def main():
     # ---------------- MD leg (value_md): the reference's benchmark protocol on the device -- fix nve + fix langevin (300 K, damp
     # 100 fs), dt 0.5 fs, moving coordinates, list rebuilt on the device every 10 steps inside the timed region
     ms_md, md_info = None, None
-    if not args.no_md:
+    if not args.no_md and nbr_kind == "full":
         from lammps_ani_b200 import nve
         masses = np.array([nve.MASS[params.symbols[int(sidx)]] for sidx in sub.species[:nlocal]])
-        md = nve.DeviceNVE(step, masses, DT_FS, temperature=300.0, seed=12345, rebuild_every=10, langevin_damp_fs=100.0)
+        t_md, damp_md = (2500.0, 50.0) if combustion else (300.0, 100.0)      # examples/combustion/in.lammps:53-57 / benchmark/in.lammps:53-59
+        md = nve.DeviceNVE(step, masses, DT_FS, temperature=t_md, seed=12345, rebuild_every=10, langevin_damp_fs=damp_md)
         for _ in range(10):
             md.advance()
         nmd = max(10, args.steps // 10 * 10)
@@ -401,8 +444,10 @@ def main():
         ke = md.kinetic()
         md_info = {"steps": nmd, "rebuilds_in_timed_region": md.rebuilds - r0, "dt_fs": DT_FS,
                    "temperature_K_after": 2.0 * ke / (3.0 * nlocal * nve.BOLTZ),
-                   "protocol": "fix nve + fix langevin 300 300 100 (uniform noise) as library kernels, neigh_modify every 10 (device rebuild), "
-                               "examples/benchmark/in.lammps:24-26,53-59"}
+                   "protocol": f"fix nve + fix langevin {t_md:g} {t_md:g} {damp_md:g} (uniform noise) as library kernels, neigh_modify every 10 "
+                               "(device rebuild), examples/benchmark/in.lammps:24-26,53-59",
+                   "note": "seeded random weights are not a physical potential: the thermostat is exercised, the trajectory means nothing"
+                           if not combustion else "real ANI-1xnr weights"}
     # ---------------- reduce over ranks (max time)
     tm = torch.tensor([ms, ms_e2e, (ms_md or 0.0) / (md_info["steps"] if md_info else 1)], dtype=torch.float64, device=dev)
     cnt = torch.tensor([float(nlocal)], dtype=torch.float64, device=dev)
@@ -459,17 +504,23 @@ def main():
                   "rebuild_note": "wall ms of one neigh rebuild: ani_build_neighbors (cell list + search on the device from device "
                                   "x) vs ani_set_neighbors_full of a ready host list (species bucketing + H2D of the list); the "
                                   "host-side construction of that list is not included in the second number"}
+        if combustion:
+            wl = (f"examples/combustion-style reactive box (config 5): {nlocal} atoms ({cells[0]} CH4 + {cells[1]} O2 at 0.25 g/cc, seeded "
+                  f"jittered-lattice placement) + {ntotal - nlocal} ghosts per GPU, ANI-1xnr (real in-tree weights, 448-long AEV; {Lc} columns "
+                  f"active){'' if args.no_repulsion else ' + RepulsionXTB'}, {M} members, fp32, {nbr_kind} neighbour list 7.1 A "
+                  f"({jl.size / nlocal:.1f} full entries/atom), replicate grid {grid[0]}x{grid[1]}x{grid[2]}")
         line = {
-            "metric": "ANI-2x water atom-timesteps/s", "value": value, "unit": "atom-timesteps/s", "n_gpus": world,
+            "metric": "ANI-1xnr combustion atom-timesteps/s" if combustion else "ANI-2x water atom-timesteps/s", "value": value,
+            "unit": "atom-timesteps/s", "n_gpus": world,
             "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": value / A100_PUBLISHED_M8 if (M == 8) else None, "dtype": "f32",
+            "scaling": "weak", "vs_baseline": value / A100_PUBLISHED_M8 if (M == 8 and not combustion) else None, "dtype": "f32",
             "data": "synthetic",
-            "config": {"workload": f"examples/water-style periodic water box, {nlocal} atoms + {ntotal - nlocal} ghosts per GPU "
+            "config": {"workload": wl if combustion else f"examples/water-style periodic water box, {nlocal} atoms + {ntotal - nlocal} ghosts per GPU "
                                    f"(lattice {cells[0]}x{cells[1]}x{cells[2]} molecules), ANI-2x geometry (1008 AEV, 7 species; {Lc} columns active for the species present), "
                                    f"{M} ensemble members, fp32, full neighbour list 7.1 A ({jl.size / nlocal:.1f}/atom), "
                                    f"replicate grid {grid[0]}x{grid[1]}x{grid[2]}; `value` = pair path on static coordinates, list "
                                    f"installed once; `value_md` = nve + langevin + device rebuild every 10 steps inside the timed region",
-                       "weights": "seeded random, ANI-2x shapes (real ANI-2x parameters unavailable offline)",
+                       "weights": "ANI-1xnr, in-tree NeuroChem ensemble" if combustion else "seeded random, ANI-2x shapes (real ANI-2x parameters unavailable offline)",
                        "mlp_mode": mode, "l2": "inputs larger than L2 (AEV rows alone exceed 126 MB); no explicit flush",
                        "vs_baseline_note": "published number is 1xA100, Kokkos, 300k water, 8 models (BASELINE.md)",
                        "setup_s": t_setup},

@@ -17,6 +17,9 @@ Layout (all little endian, no padding):
     per model m, per species s, per layer l:
         f32[dims[l+1]*dims[l]]  W  (row-major [out][in], i.e. torch.nn.Linear.weight)
         f32[dims[l+1]]          b
+    only when use_repulsion != 0 (the RepulsionXTB pair term, models/lammps_ani.py:186-192,301-330):
+        f64 cutoff (Angstrom) ; int32 cutoff_fn (0 cosine, 1 smooth order 2) ; int32 reserved
+        f64[S*S] y_ab ; f64[S*S] sqrt_alpha_ab ; f64[S*S] k_rep_ab      (row-major species x species, atomic units)
 
 Hidden layers use CELU(alpha=0.1), the last layer is linear (NeuroChem activation 9 / 6,
 /root/reference/external/ani-1xnr/model/ani-1xnr/train0/inputtrain.ipt).
@@ -50,6 +53,8 @@ class AniParams:
     # weights[m][s][l] = (W [out,in] f32, b [out] f32)
     weights: List[List[List[tuple]]] = field(default_factory=list)
     use_repulsion: bool = False
+    # RepulsionXTB tables when use_repulsion: dict(cutoff=float, cutoff_fn=0|1, y_ab=[S,S], sqrt_alpha_ab=[S,S], k_rep_ab=[S,S])
+    repulsion: dict = None
 
     @property
     def num_species(self) -> int:
@@ -89,6 +94,11 @@ class AniParams:
                     W, b = self.weights[m][s][l]
                     if W.shape != (d[l + 1], d[l]) or b.shape != (d[l + 1],):
                         raise ValueError(f"bad shape m={m} s={s} l={l}: {W.shape} {b.shape}")
+        if self.use_repulsion:
+            S = self.num_species
+            r = self.repulsion
+            if not r or any(np.asarray(r[k]).shape != (S, S) for k in ("y_ab", "sqrt_alpha_ab", "k_rep_ab")):
+                raise ValueError("use_repulsion needs the RepulsionXTB tables y_ab, sqrt_alpha_ab, k_rep_ab of shape [S, S]")
 
 
 def save(params: AniParams, path: str) -> None:
@@ -114,6 +124,11 @@ def save(params: AniParams, path: str) -> None:
                     W, b = params.weights[m][s][l]
                     f.write(np.ascontiguousarray(W, dtype="<f4").tobytes())
                     f.write(np.ascontiguousarray(b, dtype="<f4").tobytes())
+        if params.use_repulsion:
+            r = params.repulsion
+            f.write(struct.pack("<dii", float(r["cutoff"]), int(r.get("cutoff_fn", 1)), 0))
+            for k in ("y_ab", "sqrt_alpha_ab", "k_rep_ab"):
+                f.write(np.ascontiguousarray(r[k], dtype="<f8").tobytes())
 
 
 def load(path: str) -> AniParams:
@@ -151,8 +166,14 @@ def load(path: str) -> AniParams:
                 per_l.append((W, b))
             per_s.append(per_l)
         weights.append(per_s)
+    repulsion = None
+    if rep:
+        cutoff, fn, _pad = struct.unpack_from("<dii", buf, off); off += 16
+        repulsion = {"cutoff": cutoff, "cutoff_fn": fn}
+        for k in ("y_ab", "sqrt_alpha_ab", "k_rep_ab"):
+            repulsion[k] = f64(S * S).reshape(S, S)
     if off != len(buf):
         raise ValueError(f"{path}: trailing bytes ({len(buf) - off})")
-    p = AniParams(symbols, Rcr, Rca, EtaR, EtaA, Zeta, ShfR, ShfA, ShfZ, sae, dims, weights, bool(rep))
+    p = AniParams(symbols, Rcr, Rca, EtaR, EtaA, Zeta, ShfR, ShfA, ShfZ, sae, dims, weights, bool(rep), repulsion)
     p.validate()
     return p

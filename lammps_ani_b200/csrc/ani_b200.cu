@@ -22,6 +22,7 @@
 #include "mlp_tc.cuh"
 #include "nbuild.cuh"
 #include "md.cuh"
+#include "repulsion.cuh"
 
 namespace anib {
 
@@ -208,6 +209,7 @@ struct Engine : EngineBase {
   // ANI-2x's 1008) and layer 1 / dE/dAEV contract over Lc.  Exact (only zero products are skipped).  The active set only
   // grows (a superset stays exact); ANI_B200_DENSE_AEV=1 keeps all columns.
   AevConst<T> Pfull;
+  RepConst<T> rep;
   HostModel hmc;                // hm with the first-layer columns gathered (dims[s][0] = Lc); what the MLP paths upload
   uint32_t active_mask = 0;
   std::vector<int> cmap;        // species -> compact index, -1 when absent
@@ -269,6 +271,16 @@ struct Engine : EngineBase {
           col_full[P.rad_len + p * P.ang_sub + q] = Pfull.rad_len + Pfull.triu[act[a]][act[b]] * P.ang_sub + q;
         p++;
       }
+    if (hm.use_repulsion) {     // RepulsionXTB tables on the compact species indices the kernels see in x4.w
+      memset(&rep, 0, sizeof(rep));
+      for (int a = 0; a < Sp; a++)
+        for (int b = 0; b < Sp; b++) {
+          rep.y[a][b] = (T)hm.rep_y[(size_t)act[a] * hm.S + act[b]];
+          rep.sa[a][b] = (T)hm.rep_sa[(size_t)act[a] * hm.S + act[b]];
+          rep.k[a][b] = (T)hm.rep_k[(size_t)act[a] * hm.S + act[b]];
+        }
+      rep.rc = (T)hm.rep_cutoff; rep.rc2 = (T)(hm.rep_cutoff * hm.rep_cutoff); rep.fn = hm.rep_cutoff_fn;
+    }
     ld_aev = (P.aev_len + 3) / 4 * 4;
     ld_planes = (P.aev_len + 63) / 64 * 64;   // 128-byte row pitch: every TMA box row starts on a cache-line boundary
     // gathered copy of the model: only dims / W / b are read from it
@@ -727,15 +739,24 @@ struct Engine : EngineBase {
       else { set_error("unsupported number of ShfZ values (supported: 1, 2, 4, 8)"); return 1; }
       if (rc) return rc;
     }
+    // ---- (3b) RepulsionXTB pair term (models with rep_calc): forces / virial into the same arrays, energy into scalars[1]
+    const bool want_e = out_energy != nullptr;
+    if (hm.use_repulsion && nlocal > 0) {
+      if (want_e) ANIB_CUDA_OK(cudaMemsetAsync(d_scalars.as<double>() + 1, 0, sizeof(double), st));
+      repulsion_kernel<T><<<(unsigned)(((int64_t)nlocal * 32 + 255) / 256), 256, 0, st>>>(
+          rep, d_x4.as<V4>(), d_beg.as<int64_t>(), d_cnt.as<int>(), jl(), nlocal, d_force.as<T>(),
+          want_virial ? d_virial.as<double>() : nullptr, want_e ? d_scalars.as<double>() + 1 : nullptr, (T)kHartree2KcalMol);
+      c->launches++;
+    }
     if (tm) cudaEventRecord(c->ev[4], st);
     // ---- (4) reductions and outputs
-    const bool want_e = out_energy != nullptr;
     if (want_e) {
       if (nlocal > 0) {
         int nb = std::min(1024, (nlocal + 255) / 256);
         reduce_sum_stage1<<<nb, 256, 0, st>>>(d_eatom.as<double>(), nlocal, d_partial.as<double>());
         reduce_sum_stage2<<<1, 256, 0, st>>>(d_partial.as<double>(), nb, d_scalars.as<double>(), kHartree2KcalMol);
         c->launches += 2;
+        if (hm.use_repulsion) { add_scaled_scalar_kernel<<<1, 1, 0, st>>>(d_scalars.as<double>(), kHartree2KcalMol); c->launches++; }
       } else {
         ANIB_CUDA_OK(cudaMemsetAsync(d_scalars.p, 0, sizeof(double), st));
       }
@@ -952,7 +973,6 @@ int ani_ctx_create(const ani_model* model, int device, int use_num_models, int u
     return 1;
   }
   if (device >= ndev) { set_error("CUDA device ordinal out of range"); return 1; }
-  if (model->hm.use_repulsion) { set_error("models with the RepulsionXTB term are not supported yet"); return 1; }
   ANIB_CUDA_OK(cudaSetDevice(device));
   int M = use_num_models;
   if (M == -1) M = model->hm.M;   // ani.cpp:75-77

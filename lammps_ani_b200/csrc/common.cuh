@@ -25,6 +25,10 @@ struct HostModel {
   std::vector<std::vector<int>> dims;  // per species: in, h1, ..., 1
   // W[m][s][l] row-major [out][in]; b[m][s][l]
   std::vector<std::vector<std::vector<std::vector<float>>>> W, b;
+  // RepulsionXTB pair term (use_repulsion): E = sum_pairs y_ab / r * exp(-sqrt_alpha_ab r^k_ab) * fc(r), r in Bohr, E in Hartree
+  double rep_cutoff = 0.0;
+  int rep_cutoff_fn = 1;               // 0 cosine, 1 smooth (order 2)
+  std::vector<double> rep_y, rep_sa, rep_k;   // [S*S]
   int rad_len() const { return S * nR; }
   int ang_sub() const { return nA * nZ; }
   int aev_len() const { return S * nR + (S * (S + 1) / 2) * nA * nZ; }

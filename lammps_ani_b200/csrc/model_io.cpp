@@ -100,6 +100,13 @@ bool load_aniw(const std::string& path_in, HostModel& m, std::string& err) {
       }
     }
   }
+  if (m.use_repulsion) {
+    m.rep_cutoff = r.get<double>();
+    m.rep_cutoff_fn = r.get<int32_t>();
+    (void)r.get<int32_t>();
+    r.get_n(m.rep_y, (size_t)m.S * m.S); r.get_n(m.rep_sa, (size_t)m.S * m.S); r.get_n(m.rep_k, (size_t)m.S * m.S);
+    if (!r.ok || !(m.rep_cutoff > 0.0) || m.rep_cutoff_fn < 0 || m.rep_cutoff_fn > 1) { err = "'" + path + "': bad repulsion block"; return false; }
+  }
   if (!r.ok || r.off != buf.size()) { err = "'" + path + "': truncated or oversized parameter file"; return false; }
   return true;
 }

@@ -99,11 +99,14 @@ class GpuDomainStep(DomainStep):
     """Product wiring: library kernels for pack / unpack, ani_compute_device for the pair compute, everything on
     torch's current CUDA stream so NCCL and the kernels stay ordered without host synchronisation."""
 
-    def __init__(self, ani, sub, halo, device, ilist, numneigh, jlist, group=None):
+    def __init__(self, ani, sub, halo, device, ilist, numneigh, jlist, group=None, atom_index12=None):
         super().__init__(sub, halo, device, torch.float64, group)
         self.ani = ani
         ani.set_stream(torch.cuda.current_stream(device).cuda_stream)
-        ani.set_neighbors_full(sub.species, ilist, numneigh, jlist, sub.nlocal)
+        if atom_index12 is not None:                 # half-list context (`ani_neighbor half`, pair_ani.cpp:141-150)
+            ani.set_neighbors_half(sub.species, atom_index12, sub.nlocal)
+        else:
+            ani.set_neighbors_full(sub.species, ilist, numneigh, jlist, sub.nlocal)
 
     def pack_x(self, out):
         self.ani.halo_pack_x(self.x.data_ptr(), False, self.send_index.data_ptr(), self.send_shift.data_ptr(), self.nsend,

@@ -51,6 +51,49 @@ def make_water_box(cells: Tuple[int, int, int], seed: int = 12345, jitter: float
     return pos, species, box
 
 
+def _random_rotations(rng, n):
+    q = rng.standard_normal((n, 4))
+    q /= np.linalg.norm(q, axis=1, keepdims=True)
+    w, x, y, z = q.T
+    return np.stack([
+        np.stack([1 - 2 * (y * y + z * z), 2 * (x * y - z * w), 2 * (x * z + y * w)], -1),
+        np.stack([2 * (x * y + z * w), 1 - 2 * (x * x + z * z), 2 * (y * z - x * w)], -1),
+        np.stack([2 * (x * z - y * w), 2 * (y * z + x * w), 1 - 2 * (x * x + y * y)], -1)], 1)
+
+
+def make_combustion_box(n_ch4: int = 33334, seed: int = 12345, density_g_cc: float = 0.25):
+    """BASELINE.json config 5: the reference's combustion system -- n CH4 + 2n O2 at 0.25 g/cc (33 334 + 66 668 molecules =
+    300 006 atoms in a 260.715 A box: examples/combustion/prepare_system/system-300k.inp; its .data file is a missing blob).
+    packmol's random packing (tolerance 2.0 A) is replaced by a seeded jittered lattice: molecules on a random subset of the sites
+    of a simple-cubic lattice, random orientations, +-0.5 A jitter, so that atoms of different molecules stay >= 2 A apart.
+    Returns (positions [N,3], species [N] int32 in ANI-1x order H=0, C=1, N=2, O=3, box [3])."""
+    rng = np.random.default_rng(seed)
+    nmol = 3 * n_ch4
+    mass = n_ch4 * (12.0107 + 4 * 1.008) + 2 * n_ch4 * 2 * 15.999
+    L = (mass / (density_g_cc * 0.602214076)) ** (1.0 / 3.0)
+    n = int(np.ceil(nmol ** (1.0 / 3.0)))
+    a = L / n
+    if a < 5.3:
+        raise ValueError("density too high for the lattice placement (sites closer than 5.3 A)")
+    sites = rng.permutation(n ** 3)[:nmol]
+    c = (np.stack(np.unravel_index(sites, (n, n, n)), -1) + 0.5) * a + rng.uniform(-0.5, 0.5, size=(nmol, 3))
+    is_ch4 = np.zeros(nmol, dtype=bool)
+    is_ch4[rng.permutation(nmol)[:n_ch4]] = True
+    R = _random_rotations(rng, nmol)
+    t = 1.09 / np.sqrt(3.0)
+    ch4 = np.array([[0, 0, 0], [t, t, t], [t, -t, -t], [-t, t, -t], [-t, -t, t]], dtype=np.float64)
+    o2 = np.array([[0, 0, 0.604], [0, 0, -0.604]], dtype=np.float64)
+    pos, spc = [], []
+    cm = c[is_ch4]; Rm = R[is_ch4]
+    pos.append((cm[:, None, :] + np.einsum("nij,aj->nai", Rm, ch4)).reshape(-1, 3))
+    spc.append(np.tile(np.array([1, 0, 0, 0, 0], dtype=np.int32), cm.shape[0]))
+    co = c[~is_ch4]; Ro = R[~is_ch4]
+    pos.append((co[:, None, :] + np.einsum("nij,aj->nai", Ro, o2)).reshape(-1, 3))
+    spc.append(np.tile(np.array([3, 3], dtype=np.int32), co.shape[0]))
+    box = np.array([L, L, L])
+    return np.mod(np.concatenate(pos), box), np.concatenate(spc), box
+
+
 def cells_for_atoms(natoms: int) -> Tuple[int, int, int]:
     """Near-cubic lattice whose atom count is close to `natoms` (3 atoms per cell)."""
     nmol = max(1, natoms // 3)

@@ -138,6 +138,34 @@ def ani2x_constants() -> Dict:
                 ShfZ=(np.arange(4) * 2 + 1) * math.pi / 8)
 
 
+# GFN2-xTB repulsion parameters (Bannwarth, Ehlert, Grimme, JCTC 15 (2019) 1652, SI): exponent alpha and effective nuclear
+# charge Y_eff per element; k_rep = 1 when both atoms are H / He, 3/2 otherwise.  Typed in from the publication (torchani's
+# table is not in the tree): use them for tests and synthetic models; real `*_repulsion.pt` files carry their own tables.
+XTB_ALPHA = {"H": 2.213717, "C": 1.247655, "N": 1.682689, "O": 2.165712, "F": 2.421394, "S": 1.214553, "Cl": 1.577144}
+XTB_YEFF = {"H": 1.105388, "C": 4.231078, "N": 5.242592, "O": 5.784415, "F": 7.021486, "S": 14.995090, "Cl": 17.353134}
+
+
+def xtb_repulsion_tables(symbols, cutoff: float = 5.2, cutoff_fn: int = 1) -> dict:
+    """RepulsionXTB pair tables for `symbols` (torchani potentials.RepulsionXTB: y_ab = Y_a Y_b, sqrt_alpha_ab = sqrt(a_a a_b),
+    k_rep_ab = 1 for H-H else 1.5; smooth cutoff function at 5.2 A)."""
+    a = np.array([XTB_ALPHA[s] for s in symbols])
+    y = np.array([XTB_YEFF[s] for s in symbols])
+    light = np.array([s in ("H", "He") for s in symbols])
+    return {"cutoff": float(cutoff), "cutoff_fn": int(cutoff_fn), "y_ab": np.outer(y, y), "sqrt_alpha_ab": np.sqrt(np.outer(a, a)),
+            "k_rep_ab": np.where(np.outer(light, light), 1.0, 1.5)}
+
+
+def with_repulsion(p: AniParams, **kw) -> AniParams:
+    """The same model with the RepulsionXTB term switched on (what `ani2x_repulsion.pt` / `ani1x_nr_repulsion.pt` are to
+    `ani2x.pt` / `ani1x_nr.pt`, examples/combustion/README.md:4,10)."""
+    import copy
+    q = copy.copy(p)
+    q.use_repulsion = True
+    q.repulsion = xtb_repulsion_tables(p.symbols, **kw)
+    q.validate()
+    return q
+
+
 def synthetic_ani2x(seed: int = 2024, num_models: int = 8, weight_scale: float = 1.0) -> AniParams:
     """ANI-2x geometry (1008-long AEV, 7 species, 8 members) with seeded random weights.
 

@@ -263,8 +263,20 @@ def read_torchscript_params(pt_path: str):
     # The reference always stores a `use_repulsion` bool AND a dummy `rep_calc = RepulsionXTB(("H"))` submodule, also when the
     # term is off (models/lammps_ani.py:91-99): only the VALUE of the top-level attribute says whether it is used.
     rep = bool(flat.get("use_repulsion", False))
+    repulsion = None
+    if rep:
+        # RepulsionXTB buffers (torchani potentials.RepulsionXTB; attribute names as in torchani 2.x -- not verifiable offline)
+        tabs = {}
+        for name in ("y_ab", "sqrt_alpha_ab", "k_rep_ab"):
+            k, v = _find({kk: vv for kk, vv in flat.items() if kk.startswith("rep_calc.")}, name)
+            if v is None or np.asarray(v).shape != (S, S):
+                raise ValueError(f"{pt_path}: use_repulsion is set but rep_calc.{name} [{S},{S}] was not found")
+            tabs[name] = np.asarray(v, dtype=np.float64)
+        _, cut = _find({kk: vv for kk, vv in flat.items() if kk.startswith("rep_calc.")}, "cutoff")
+        fn_names = " ".join(str(v) for kk, v in flat.items() if kk.startswith("rep_calc.") and isinstance(v, str)).lower()
+        repulsion = dict(cutoff=_scalar(cut) if cut is not None else 5.2, cutoff_fn=0 if "cosine" in fn_names else 1, **tabs)
     p = AniParams(symbols, consts["Rcr"], consts["Rca"], float(consts["EtaR"][0]), float(consts["EtaA"][0]),
                   float(consts["Zeta"][0]), consts["ShfR"], consts["ShfA"], consts["ShfZ"], sae, dims, weights,
-                  use_repulsion=bool(rep))
+                  use_repulsion=bool(rep), repulsion=repulsion)
     p.validate()
     return p

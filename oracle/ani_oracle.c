@@ -41,6 +41,8 @@
 
 typedef struct {
   int S, nR, nA, nZ, M, maxl, use_rep;
+  /* RepulsionXTB pair term (models/lammps_ani.py:186-192,301-330; torchani potentials.RepulsionXTB, not in tree) */
+  double rep_cutoff; int rep_fn; const double *rep_y, *rep_sa, *rep_k;
   double Rcr, Rca, EtaR, EtaA, Zeta;
   double *ShfR, *ShfA, *ShfZ, *sae;
   int nlayers[MAXS];
@@ -91,6 +93,12 @@ omodel* ani_oracle_model_load(const char* path) {
         m->W[idx] = (float*)(buf + off); off += 4L * m->dims[s][l] * m->dims[s][l + 1];
         m->b[idx] = (float*)(buf + off); off += 4L * m->dims[s][l + 1];
       }
+  if (m->use_rep) {
+    memcpy(&m->rep_cutoff, buf + off, 8); m->rep_fn = rd_i32(buf + off + 8); off += 16;
+    m->rep_y = (const double*)(buf + off); off += 8L * m->S * m->S;
+    m->rep_sa = (const double*)(buf + off); off += 8L * m->S * m->S;
+    m->rep_k = (const double*)(buf + off); off += 8L * m->S * m->S;
+  }
   if (off != n) { fprintf(stderr, "ani_oracle: trailing bytes in %s\n", path); }
   m->rad_len = m->S * m->nR;
   m->ang_sub = m->nA * m->nZ;
@@ -293,6 +301,36 @@ static double mlp_atom(const omodel* m, int nm, int s, const double* G, double* 
   return etot * inv;
 }
 
+/* RepulsionXTB pair energy (Hartree) and its derivative with respect to r (Angstrom):
+ *   e(r) = y_ab / r_b * exp(-sqrt_alpha_ab * r_b^k_ab) * fc(r),  r_b = r in Bohr   (GFN2-xTB repulsion; torchani potentials.RepulsionXTB)
+ *   fc: 1 = exp(1 - 1 / (1 - (r/Rc)^2)) ("smooth", order 2);  0 = 0.5 cos(pi r / Rc) + 0.5.
+ * Every list ENTRY (centre i local, neighbour j) carries half of the pair: a local-local pair appears in both rows, a pair with
+ * a ghost only once -- torchani halves pairs that touch a ghost (`ghost_flags`), the other half belongs to the neighbouring
+ * subdomain / periodic image.  Restated from the published functional form: the torchani source is not in the tree and no model
+ * file with `rep_calc` is available, so this term is PARITY UNPINNED. */
+#define ANGSTROM_TO_BOHR 1.8897261258369282
+static double rep_pair(const omodel* m, int sa_, int sb_, double r, double* de_dr) {
+  const double Rc = m->rep_cutoff;
+  if (r > Rc || r <= 0.0) { *de_dr = 0.0; return 0.0; }
+  const double y = m->rep_y[sa_ * m->S + sb_], sa = m->rep_sa[sa_ * m->S + sb_], k = m->rep_k[sa_ * m->S + sb_];
+  const double rb = r * ANGSTROM_TO_BOHR;
+  const double p = pow(rb, k);
+  const double base = y / rb * exp(-sa * p);
+  const double dbase = base * (-1.0 / r - sa * k * p / r);
+  double fc, dfc;
+  if (m->rep_fn == 1) {
+    const double t = (r / Rc) * (r / Rc);
+    if (t >= 1.0) { *de_dr = 0.0; return 0.0; }
+    fc = exp(1.0 - 1.0 / (1.0 - t));
+    dfc = fc * (-1.0 / ((1.0 - t) * (1.0 - t))) * (2.0 * r / (Rc * Rc));
+  } else {
+    fc = 0.5 * cos(M_PI * r / Rc) + 0.5;
+    dfc = -0.5 * M_PI / Rc * sin(M_PI * r / Rc);
+  }
+  *de_dr = dbase * fc + base * dfc;
+  return base * fc;
+}
+
 /* Main entry.  Neighbours of LOCAL atoms come as CSR (nbr_off[nlocal+1], nbr[]).
  * species[ntotal] in 0..S-1 (ghosts keep their real species; they are "padding" only for the energy sum).
  * Outputs (Hartree, Hartree/Angstrom): energy, forces[ntotal*3], eatom[nlocal] (may be NULL),
@@ -340,6 +378,23 @@ int ani_oracle_compute(const omodel* m, int num_models_used, int radial_filter, 
     for (int i = 0; i < nlocal; i++) {
       int si = species[i];
       if (si < 0 || si >= m->S) { bad = 1; continue; }
+      if (m->use_rep && !aev_only) {      /* pair repulsion over the raw list entries (its own cutoff, no AEV filter) */
+        for (int64_t p = nbr_off[i]; p < nbr_off[i + 1]; p++) {
+          int j = nbr[p];
+          if (species[j] < 0 || species[j] >= m->S) continue;
+          double d[3] = {x[3 * j] - x[3 * i], x[3 * j + 1] - x[3 * i + 1], x[3 * j + 2] - x[3 * i + 2]};
+          double r = sqrt(d[0] * d[0] + d[1] * d[1] + d[2] * d[2]), de;
+          double e = rep_pair(m, si, species[j], r, &de);
+          if (e == 0.0 && de == 0.0) continue;
+          ethr[tid] += 0.5 * e;
+          for (int c = 0; c < 3; c++) {
+            double g = 0.5 * de * d[c] / r;     /* dE/dd_c */
+            f[3 * i + c] += g;
+            f[3 * j + c] -= g;
+            for (int c2 = 0; c2 < 3; c2++) v[3 * c + c2] -= g * d[c2];
+          }
+        }
+      }
       int nn = 0;
       for (int64_t p = nbr_off[i]; p < nbr_off[i + 1]; p++) {
         int j = nbr[p];

@@ -317,3 +317,23 @@ def test_compute_device_matches_oracle(ANI, ani2x_synth_path, x_is_float, f_is_f
     ani.synchronize()
     df2 = (f - f0).double().cpu().numpy()
     assert np.abs(df2 - 2.0 * ref["forces"]).max() <= 2 * F_TOL_FP32 + (4e-5 if f_is_float else 0.0)
+
+
+@pytest.mark.parametrize("repulsion", [False, True])
+def test_combustion_config5_half_list(ANI, ani1xnr_path, tmp_path, repulsion):
+    """BASELINE.json config 5 at parity size: CH4 + 2 O2 at 0.25 g/cc (19 998 atoms of the reference's 300 006-atom recipe,
+    examples/combustion/prepare_system/system-300k.inp), real ANI-1xnr weights, HALF neighbour list (`ani_neighbor half`,
+    13 stored pairs per atom), fp32, with and without the RepulsionXTB term of the `*_repulsion` models; H, C, O present:
+    288 active AEV columns, a 2 222-atom C bucket."""
+    from lammps_ani_b200 import aniw, extract
+    path = ani1xnr_path
+    if repulsion:
+        path = str(tmp_path / "ani1x_nr_repulsion.aniw")
+        aniw.save(extract.with_repulsion(aniw.load(ani1xnr_path)), path)
+    x, sp, box = domain.make_combustion_box(2222, seed=3)
+    sub = domain.decompose(x, sp, box)[0]
+    idx = domain.half_neighbor_list(sub.x, sub.nlocal)
+    assert 12.0 < idx.shape[1] / sub.nlocal < 14.5
+    ref = OracleANI(path).compute_half(sub.species, sub.x, idx, sub.nlocal, single_coords=True)
+    out = ANI(path, 0, -1, True, False, True).compute(sub.species, sub.x, idx, nlocal=sub.nlocal, ago=0, atomic=True, vflag=True)
+    check(out, ref, True, sub.nlocal)

@@ -57,12 +57,13 @@ class _Stacked(torch.nn.Module):
 
 
 class _Rep(torch.nn.Module):
-    """Stand-in for the dummy RepulsionXTB(("H")) every exported LammpsANI carries (models/lammps_ani.py:91-99)."""
-    def __init__(self):
+    """Stand-in for RepulsionXTB: the dummy RepulsionXTB(("H")) every exported LammpsANI carries (models/lammps_ani.py:91-99),
+    or real tables when the term is on."""
+    def __init__(self, tabs=None):
         super().__init__()
-        self.register_buffer("y_ab", torch.ones(1, 1))
-        self.register_buffer("sqrt_alpha_ab", torch.ones(1, 1))
-        self.cutoff: float = 5.1
+        for name in ("y_ab", "sqrt_alpha_ab", "k_rep_ab"):
+            self.register_buffer(name, torch.ones(1, 1) if tabs is None else torch.tensor(tabs[name]))
+        self.cutoff: float = 5.2
 
 
 class _Top(torch.nn.Module):
@@ -71,7 +72,7 @@ class _Top(torch.nn.Module):
         self.aev_computer = _AEV(p)
         self.energy_shifter = _Shifter(p)
         self.use_repulsion: bool = use_repulsion
-        self.rep_calc = _Rep()
+        self.rep_calc = _Rep(extract.xtb_repulsion_tables(p.symbols) if use_repulsion else None)
         if stacked == "dict":      # BmmEnsemble container keyed by element symbol: archive order is NOT alphabetical order
             self.neural_networks = torch.nn.ModuleDict({sym: _Stacked(p, s) for s, sym in enumerate(p.symbols)})
         elif stacked:
@@ -123,4 +124,10 @@ def test_use_repulsion_is_read_from_the_attribute_value(ani1xnr_path, tmp_path):
     p = aniw.load(ani1xnr_path)
     pt = str(tmp_path / "rep.pt")
     torch.jit.save(torch.jit.script(_Top(p, True, use_repulsion=True)), pt)
-    assert ptreader.read_torchscript_params(pt).use_repulsion
+    q = ptreader.read_torchscript_params(pt)
+    assert q.use_repulsion and q.repulsion["cutoff"] == 5.2
+    assert np.allclose(q.repulsion["y_ab"], extract.xtb_repulsion_tables(p.symbols)["y_ab"])
+    out = str(tmp_path / "rep.aniw")
+    aniw.save(q, out)
+    r = aniw.load(out)
+    assert r.use_repulsion and np.array_equal(r.repulsion["k_rep_ab"], q.repulsion["k_rep_ab"])
