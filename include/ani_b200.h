@@ -155,6 +155,25 @@ int ani_md_sum_mv2(ani_ctx* ctx, const double* v_dev, const double* mass_dev, in
 int ani_md_ghost_x(ani_ctx* ctx, double* x_dev, const int* owner_dev, const double* shift_dev, int nlocal, int nghost);
 int ani_md_fold_ghost_f(ani_ctx* ctx, double* f_dev, const int* owner_dev, int nlocal, int nghost);
 
+/* ---- ghost exchange of a domain-decomposed run, inside the library: CommBrick::forward_comm and
+ * reverse_comm(Pair*) (comm_brick.cpp:538-593,1023-1053; KOKKOS/comm_kokkos.cpp:187-360) + pair_ani.cpp:461-484 as one pack
+ * kernel, one ncclSend / ncclRecv group over NVLink straight into / out of the ghost slab, one fold kernel -- all on the
+ * context's stream, no host synchronisation.
+ *   ani_halo_unique_id   : rank 0 creates the ncclUniqueId (128 bytes); the caller distributes it (MPI_Bcast / any control plane).
+ *   ani_halo_plan_create : collective over the nranks callers.  send_index[nsend] local atom index and send_shift[nsend][3]
+ *                          displacement added on the way out, concatenated in DESTINATION-rank order (send_counts[nranks]); the
+ *                          ghosts of x / f, rows nlocal.., are ordered by SOURCE rank (recv_counts[nranks]).  A rank's send to
+ *                          itself (periodic images) is a device copy.  nranks == 1 needs no id and no NCCL.
+ *   ani_halo_forward     : ghost rows of x_dev <- owners' positions (+ shift).      [ntotal][3] doubles, device
+ *   ani_halo_reverse     : f_dev[owner] += ghost rows of f_dev.                                                                 */
+typedef struct ani_halo_plan ani_halo_plan;
+int ani_halo_unique_id(char out[128]);
+int ani_halo_plan_create(ani_ctx* ctx, const char unique_id[128], int nranks, int rank, int nlocal, const int64_t* send_index,
+                         const double* send_shift, const int* send_counts, const int* recv_counts, ani_halo_plan** out);
+void ani_halo_plan_destroy(ani_halo_plan* plan);
+int ani_halo_forward(ani_halo_plan* plan, double* x_dev);
+int ani_halo_reverse(ani_halo_plan* plan, double* f_dev);
+
 /* Device-memory helpers on the context's device and stream, for callers that do not link the CUDA runtime (the LAMMPS
  * plugin's device-resident mode): alloc / free, blocking upload / download ordered after everything queued on the context's
  * stream (download also reports pending device-side error flags), asynchronous zero fill. */

@@ -9,7 +9,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libani_b200.so")
 SOURCES = ["ani_b200.cu", "model_io.cpp"]
-HEADERS = ["common.cuh", "aev.cuh", "mlp_simt.cuh", "mlp_tc.cuh", "mlp_f16.cuh", "mlp_f16_fused.cuh", "nbuild.cuh", "aev2.cuh", "misc.cuh", "md.cuh", "repulsion.cuh", "../../include/ani_b200.h"]
+HEADERS = ["common.cuh", "aev.cuh", "mlp_simt.cuh", "mlp_tc.cuh", "mlp_f16.cuh", "mlp_f16_fused.cuh", "nbuild.cuh", "aev2.cuh", "misc.cuh", "md.cuh", "repulsion.cuh", "halo.cuh", "../../include/ani_b200.h"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "--use_fast_math",
               "-Xcompiler", "-fPIC", "-shared", "-ccbin", "/usr/bin/g++"]
 
@@ -26,7 +26,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
         return LIB
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
     cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + [os.path.join(CSRC, f) for f in SOURCES] + \
-          ["-o", LIB, "-lcudart", "-lcuda"]
+          ["-o", LIB, "-lcudart", "-lcuda", "-ldl"]
     subprocess.check_call(cmd)
     return LIB
 

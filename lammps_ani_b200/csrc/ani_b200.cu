@@ -23,6 +23,7 @@
 #include "nbuild.cuh"
 #include "md.cuh"
 #include "repulsion.cuh"
+#include "halo.cuh"
 
 namespace anib {
 
@@ -145,6 +146,11 @@ using namespace anib;
 
 struct ani_model {
   HostModel hm;
+};
+
+struct ani_halo_plan {
+  anib::HaloPlan p;
+  ani_ctx* ctx = nullptr;
 };
 
 struct ani_ctx {
@@ -1407,6 +1413,122 @@ int ani_md_fold_ghost_f(ani_ctx* c, double* f_dev, const int* owner_dev, int nlo
   ANIB_CUDA_OK(cudaSetDevice(c->device));
   md_fold_ghost_kernel<<<(unsigned)(((int64_t)nghost * 3 + 255) / 256), 256, 0, c->stream>>>(f_dev, owner_dev, nlocal, nghost);
   ANIB_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+// ---- ghost exchange inside the library (halo.cuh)
+int ani_halo_unique_id(char out[128]) {
+  if (!out) { set_error("ani_halo_unique_id: null argument"); return 1; }
+  NcclApi& n = nccl_api();
+  if (!n.ok) { set_error("libnccl.so.2 could not be loaded"); return 1; }
+  ncclUniqueId id;
+  ANIB_NCCL_OK(n.GetUniqueId(&id));
+  memcpy(out, id.internal, 128);
+  return 0;
+}
+
+int ani_halo_plan_create(ani_ctx* c, const char unique_id[128], int nranks, int rank, int nlocal, const int64_t* send_index,
+                         const double* send_shift, const int* send_counts, const int* recv_counts, ani_halo_plan** out) {
+  if (!c || !out || !send_counts || !recv_counts || nranks < 1 || rank < 0 || rank >= nranks) { set_error("ani_halo_plan_create: bad argument"); return 1; }
+  ANIB_CUDA_OK(cudaSetDevice(c->device));
+  std::unique_ptr<ani_halo_plan> hp(new ani_halo_plan());
+  HaloPlan& p = hp->p;
+  hp->ctx = c;
+  p.device = c->device; p.nranks = nranks; p.rank = rank; p.nlocal = nlocal; p.stream = c->stream;
+  p.send_off.assign(nranks + 1, 0); p.recv_off.assign(nranks + 1, 0);
+  for (int r = 0; r < nranks; r++) {
+    if (send_counts[r] < 0 || recv_counts[r] < 0) { set_error("ani_halo_plan_create: negative count"); return 1; }
+    p.send_off[r + 1] = p.send_off[r] + send_counts[r];
+    p.recv_off[r + 1] = p.recv_off[r] + recv_counts[r];
+  }
+  p.nsend = p.send_off[nranks]; p.nghost = p.recv_off[nranks];
+  if (p.nsend > 0 && (!send_index || !send_shift)) { set_error("ani_halo_plan_create: null send arrays"); return 1; }
+  if (send_counts[rank] != recv_counts[rank]) { set_error("ani_halo_plan_create: self send / receive counts differ"); return 1; }
+  const size_t ns = (size_t)std::max<int64_t>(p.nsend, 1);
+  ANIB_CUDA_OK(cudaMalloc((void**)&p.d_send_index, ns * sizeof(int64_t)));
+  ANIB_CUDA_OK(cudaMalloc((void**)&p.d_send_shift, ns * 3 * sizeof(double)));
+  ANIB_CUDA_OK(cudaMalloc((void**)&p.d_send_buf, ns * 3 * sizeof(double)));
+  if (p.nsend > 0) {
+    ANIB_CUDA_OK(cudaMemcpy(p.d_send_index, send_index, (size_t)p.nsend * sizeof(int64_t), cudaMemcpyHostToDevice));
+    ANIB_CUDA_OK(cudaMemcpy(p.d_send_shift, send_shift, (size_t)p.nsend * 3 * sizeof(double), cudaMemcpyHostToDevice));
+  }
+  if (nranks > 1) {
+    NcclApi& n = nccl_api();
+    if (!n.ok) { set_error("libnccl.so.2 could not be loaded"); return 1; }
+    if (!unique_id) { set_error("ani_halo_plan_create: a ncclUniqueId is needed for more than one rank"); return 1; }
+    ncclUniqueId id;
+    memcpy(id.internal, unique_id, 128);
+    ANIB_NCCL_OK(n.CommInitRank(&p.comm, nranks, id, rank));
+  }
+  *out = hp.release();
+  return 0;
+}
+
+void ani_halo_plan_destroy(ani_halo_plan* hp) {
+  if (!hp) return;
+  HaloPlan& p = hp->p;
+  cudaSetDevice(p.device);
+  cudaStreamSynchronize(hp->ctx->stream);
+  if (p.comm && nccl_api().ok) nccl_api().CommDestroy(p.comm);
+  cudaFree(p.d_send_index); cudaFree(p.d_send_shift); cudaFree(p.d_send_buf);
+  delete hp;
+}
+
+// ghost positions: x[nlocal + ...] <- owners' x (+ periodic shift), blocks ordered by source rank
+int ani_halo_forward(ani_halo_plan* hp, double* x_dev) {
+  if (!hp || !x_dev) { set_error("ani_halo_forward: null argument"); return 1; }
+  HaloPlan& p = hp->p;
+  cudaStream_t st = hp->ctx->stream;
+  ANIB_CUDA_OK(cudaSetDevice(p.device));
+  if (p.nsend > 0) {
+    halo_pack_kernel<double><<<(unsigned)((p.nsend * 3 + 255) / 256), 256, 0, st>>>(x_dev, p.d_send_index, p.d_send_shift, p.nsend, p.d_send_buf);
+    ANIB_CUDA_OK(cudaGetLastError());
+  }
+  double* ghosts = x_dev + (size_t)p.nlocal * 3;
+  const int64_t self = p.send_off[p.rank + 1] - p.send_off[p.rank];
+  if (self > 0)       // periodic self images: a device copy, no communication
+    ANIB_CUDA_OK(cudaMemcpyAsync(ghosts + p.recv_off[p.rank] * 3, p.d_send_buf + p.send_off[p.rank] * 3, (size_t)self * 3 * sizeof(double),
+                                 cudaMemcpyDeviceToDevice, st));
+  if (p.nranks > 1) {
+    NcclApi& n = nccl_api();
+    ANIB_NCCL_OK(n.GroupStart());
+    for (int r = 0; r < p.nranks; r++) {
+      if (r == p.rank) continue;
+      const int64_t ns = p.send_off[r + 1] - p.send_off[r], nr = p.recv_off[r + 1] - p.recv_off[r];
+      if (ns > 0) ANIB_NCCL_OK(n.Send(p.d_send_buf + p.send_off[r] * 3, (size_t)ns * 3, ncclDouble, r, p.comm, st));
+      if (nr > 0) ANIB_NCCL_OK(n.Recv(ghosts + p.recv_off[r] * 3, (size_t)nr * 3, ncclDouble, r, p.comm, st));
+    }
+    ANIB_NCCL_OK(n.GroupEnd());
+  }
+  return 0;
+}
+
+// ghost forces: f[owner] += f[ghost]   (newton off: the pair style folds its own ghost forces, pair_ani.cpp:197-201)
+int ani_halo_reverse(ani_halo_plan* hp, double* f_dev) {
+  if (!hp || !f_dev) { set_error("ani_halo_reverse: null argument"); return 1; }
+  HaloPlan& p = hp->p;
+  cudaStream_t st = hp->ctx->stream;
+  ANIB_CUDA_OK(cudaSetDevice(p.device));
+  double* ghosts = f_dev + (size_t)p.nlocal * 3;
+  const int64_t self = p.send_off[p.rank + 1] - p.send_off[p.rank];
+  if (self > 0)
+    ANIB_CUDA_OK(cudaMemcpyAsync(p.d_send_buf + p.send_off[p.rank] * 3, ghosts + p.recv_off[p.rank] * 3, (size_t)self * 3 * sizeof(double),
+                                 cudaMemcpyDeviceToDevice, st));
+  if (p.nranks > 1) {
+    NcclApi& n = nccl_api();
+    ANIB_NCCL_OK(n.GroupStart());
+    for (int r = 0; r < p.nranks; r++) {
+      if (r == p.rank) continue;
+      const int64_t ns = p.send_off[r + 1] - p.send_off[r], nr = p.recv_off[r + 1] - p.recv_off[r];
+      if (nr > 0) ANIB_NCCL_OK(n.Send(ghosts + p.recv_off[r] * 3, (size_t)nr * 3, ncclDouble, r, p.comm, st));
+      if (ns > 0) ANIB_NCCL_OK(n.Recv(p.d_send_buf + p.send_off[r] * 3, (size_t)ns * 3, ncclDouble, r, p.comm, st));
+    }
+    ANIB_NCCL_OK(n.GroupEnd());
+  }
+  if (p.nsend > 0) {
+    halo_unpack_add_kernel<double><<<(unsigned)((p.nsend * 3 + 255) / 256), 256, 0, st>>>(f_dev, p.d_send_index, p.d_send_buf, p.nsend);
+    ANIB_CUDA_OK(cudaGetLastError());
+  }
   return 0;
 }
 

@@ -68,6 +68,12 @@ def load_library():
     L.ani_md_sum_mv2.argtypes = [vp, vp, vp, i32, dp]
     L.ani_md_ghost_x.argtypes = [vp, vp, vp, vp, i32, i32]
     L.ani_md_fold_ghost_f.argtypes = [vp, vp, vp, i32, i32]
+    L.ani_halo_unique_id.argtypes = [C.c_char_p]
+    L.ani_halo_plan_create.argtypes = [vp, C.c_char_p, i32, i32, i32, vp, vp, vp, vp, C.POINTER(vp)]
+    L.ani_halo_plan_destroy.argtypes = [vp]
+    L.ani_halo_plan_destroy.restype = None
+    L.ani_halo_forward.argtypes = [vp, vp]
+    L.ani_halo_reverse.argtypes = [vp, vp]
     L.ani_halo_pack_x.argtypes = [vp, vp, i32, vp, vp, i64, vp]
     L.ani_halo_unpack_add_f.argtypes = [vp, vp, i32, vp, vp, i64]
     for name in ("ani_model_load", "ani_model_info", "ani_ctx_create", "ani_ctx_set_mlp_mode", "ani_ctx_set_option", "ani_ctx_set_stream",
@@ -75,7 +81,8 @@ def load_library():
                  "ani_set_neighbors_half", "ani_set_neighbors_table", "ani_device_count", "ani_compute",
                  "ani_compute_device", "ani_debug_get_aev", "ani_halo_pack_x", "ani_halo_unpack_add_f", "ani_build_neighbors",
                  "ani_debug_get_neighbors", "ani_md_nve_initial", "ani_md_nve_final", "ani_md_langevin", "ani_md_sum_mv2",
-                 "ani_md_ghost_x", "ani_md_fold_ghost_f"):
+                 "ani_md_ghost_x", "ani_md_fold_ghost_f", "ani_halo_unique_id", "ani_halo_plan_create", "ani_halo_forward",
+                 "ani_halo_reverse"):
         getattr(L, name).restype = i32
     _lib = L
     return L
@@ -89,6 +96,7 @@ EXPORTED_SYMBOLS = [
     "ani_device_count", "ani_build_neighbors", "ani_debug_get_neighbors", "ani_ctx_release_host_buffers", "ani_ctx_set_option",
     "ani_md_nve_initial", "ani_md_nve_final", "ani_md_langevin", "ani_md_sum_mv2", "ani_md_ghost_x", "ani_md_fold_ghost_f",
     "ani_dev_alloc", "ani_dev_free", "ani_dev_upload", "ani_dev_download", "ani_dev_zero",
+    "ani_halo_unique_id", "ani_halo_plan_create", "ani_halo_plan_destroy", "ani_halo_forward", "ani_halo_reverse",
 ]
 
 
@@ -293,6 +301,33 @@ class ANI:
         out = C.c_double()
         _check(self._L.ani_md_sum_mv2(self._ctx, C.c_void_p(v_ptr), C.c_void_p(mass_ptr), int(n), C.byref(out)))
         return out.value
+
+    # ---- ghost exchange inside the library (NCCL send / recv groups on the context's stream)
+    @staticmethod
+    def halo_unique_id() -> bytes:
+        buf = C.create_string_buffer(128)
+        _check(load_library().ani_halo_unique_id(buf))
+        return buf.raw
+
+    def halo_plan_create(self, unique_id: Optional[bytes], nranks: int, rank: int, nlocal: int, send_index, send_shift, send_counts,
+                         recv_counts):
+        si = np.ascontiguousarray(send_index, dtype=np.int64)
+        sh = np.ascontiguousarray(send_shift, dtype=np.float64).reshape(-1, 3)
+        sc = np.ascontiguousarray(send_counts, dtype=np.int32)
+        rc = np.ascontiguousarray(recv_counts, dtype=np.int32)
+        plan = C.c_void_p()
+        _check(self._L.ani_halo_plan_create(self._ctx, unique_id, int(nranks), int(rank), int(nlocal), _ptr(si), _ptr(sh), _ptr(sc), _ptr(rc),
+                                            C.byref(plan)))
+        return plan
+
+    def halo_plan_destroy(self, plan):
+        self._L.ani_halo_plan_destroy(plan)
+
+    def halo_forward(self, plan, x_ptr):
+        _check(self._L.ani_halo_forward(plan, C.c_void_p(x_ptr)))
+
+    def halo_reverse(self, plan, f_ptr):
+        _check(self._L.ani_halo_reverse(plan, C.c_void_p(f_ptr)))
 
     def halo_pack_x(self, x_ptr, is_float, index_ptr, shift_ptr, n, out_ptr):
         _check(self._L.ani_halo_pack_x(self._ctx, C.c_void_p(x_ptr), int(is_float), C.c_void_p(index_ptr),

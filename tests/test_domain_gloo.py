@@ -14,6 +14,17 @@ import torch.multiprocessing as mp
 from lammps_ani_b200 import domain
 from lammps_ani_b200.ddstep import DomainStep
 
+class GlooDomainStep(DomainStep):
+    """torch.distributed transport for the CPU test: one all_to_all_single each way, the same destination-ordered send layout and
+    source-ordered ghost layout the library's NCCL plan uses (csrc/halo.cuh)."""
+
+    def exchange_forward(self, ghosts, packed):
+        dist.all_to_all_single(ghosts, packed, output_split_sizes=self.recv_rows, input_split_sizes=self.send_rows)
+
+    def exchange_reverse(self, packed, ghosts):
+        dist.all_to_all_single(packed, ghosts, output_split_sizes=self.send_rows, input_split_sizes=self.recv_rows)
+
+
 GRID = (2, 1, 1)
 CELLS = (6, 5, 5)
 
@@ -49,7 +60,7 @@ def _worker(rank, world, port, model, out_dir):
         subs = domain.decompose(x, sp, box, GRID)
         plans = domain.halo_plans(subs, x)
         sub, halo = subs[rank], _halo_from_plan(plans[rank])
-        step = DomainStep(sub, halo, torch.device("cpu"))
+        step = GlooDomainStep(sub, halo, torch.device("cpu"), world=world)
         # move the LOCAL atoms only: the ghosts are stale until the forward halo refreshes them
         nl = sub.nlocal
         step.x[:nl] += torch.tensor(_displacement(sub.global_id[:nl]))

@@ -337,3 +337,35 @@ def test_combustion_config5_half_list(ANI, ani1xnr_path, tmp_path, repulsion):
     ref = OracleANI(path).compute_half(sub.species, sub.x, idx, sub.nlocal, single_coords=True)
     out = ANI(path, 0, -1, True, False, True).compute(sub.species, sub.x, idx, nlocal=sub.nlocal, ago=0, atomic=True, vflag=True)
     check(out, ref, True, sub.nlocal)
+
+
+def test_library_halo_plan_matches_torch_reference(ANI, ani2x_synth_path):
+    """ani_halo_forward / ani_halo_reverse (csrc/halo.cuh: halo_pack_kernel, the self-image device copy, halo_unpack_add_kernel)
+    on one rank against the torch index-op reference of ddstep.DomainStep: ghost positions after moving the local atoms, and
+    the fold of ghost forces onto their owners (an owner appears several times: atomics)."""
+    import torch
+    from lammps_ani_b200 import ddstep
+    x, sp, box = domain.make_water_box((5, 4, 4), seed=8)
+    sub = domain.decompose(x, sp, box)[0]
+    halo = domain.replica_halo(sub, box, (1, 1, 1), 0)
+    il, nn, jl = domain.full_neighbor_list(sub.x, sub.nlocal)
+    ani = ANI(ani2x_synth_path, 0, -1, True, True, True)
+    dev = torch.device("cuda", 0)
+    g = ddstep.GpuDomainStep(ani, sub, halo, dev, il, nn, jl)
+    c = ddstep.DomainStep(sub, halo, torch.device("cpu"))
+    rng = np.random.default_rng(1)
+    dx = torch.tensor(rng.normal(scale=0.05, size=(sub.nlocal, 3)))
+    g.x[:sub.nlocal] += dx.to(dev); c.x[:sub.nlocal] += dx
+    g.forward_halo(); c.forward_halo()
+    ani.synchronize()
+    assert torch.equal(g.x.cpu(), c.x)
+    ff = torch.tensor(rng.normal(size=(sub.ntotal, 3)))
+    g.f.copy_(ff.to(dev)); c.f.copy_(ff)
+    g.reverse_halo(); c.reverse_halo()
+    ani.synchronize()
+    assert (g.f[:sub.nlocal].cpu() - c.f[:sub.nlocal]).abs().max() < 1e-12
+    # and the single-domain emulation used by bench.py's multi-GPU force check
+    g.x[:sub.nlocal] += 0.01; c.x[:sub.nlocal] += 0.01
+    g.forward_halo_local(); c.forward_halo()
+    ani.synchronize()
+    assert (g.x.cpu() - c.x).abs().max() < 1e-12
