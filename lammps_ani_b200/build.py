@@ -52,6 +52,30 @@ def build_plugin(force: bool = False) -> str:
     return PLUGIN
 
 
+def check_kokkos_branch() -> None:
+    """Type-check the `-DLMP_KOKKOS` branch of the pair style (`ani/kk` on Kokkos views, reference: src/pair_ani_kokkos.cpp:67-235)
+    against the in-tree LAMMPS KOKKOS package and its vendored Kokkos 3.7.01, Serial backend, `g++ -fsyntax-only`.  The branch
+    cannot be RUN here: a KOKKOS LAMMPS needs Kokkos's own build system, and Kokkos 3.7.01 has no sm_100 target."""
+    import tempfile
+    lammps = os.path.dirname(LAMMPS_SRC)
+    kk = os.path.join(lammps, "lib", "kokkos")
+    if not os.path.exists(os.path.join(kk, "core", "src", "Kokkos_Core.hpp")):
+        raise RuntimeError(f"Kokkos headers not found under {kk}")
+    with tempfile.TemporaryDirectory() as cfg:
+        with open(os.path.join(cfg, "KokkosCore_config.h"), "w") as f:
+            f.write("#pragma once\n#define KOKKOS_VERSION 30701\n#define KOKKOS_ENABLE_SERIAL\n#define KOKKOS_ENABLE_CXX17\n"
+                    "#define KOKKOS_ENABLE_COMPLEX_ALIGN\n#define KOKKOS_ENABLE_LIBDL\n#define KOKKOS_ENABLE_IMPL_DESUL_ATOMICS\n")
+        for name, body in (("DeclareBackend", "#include <decl/Kokkos_Declare_SERIAL.hpp>\n"), ("FwdBackend", "#include <fwd/Kokkos_Fwd_SERIAL.hpp>\n"),
+                           ("SetupBackend", ""), ("PostInclude", "")):
+            with open(os.path.join(cfg, f"KokkosCore_Config_{name}.hpp"), "w") as f:
+                f.write(body)
+        inc = [cfg, f"{kk}/core/src", f"{kk}/containers/src", f"{kk}/algorithms/src", f"{kk}/tpls/desul/include", f"{LAMMPS_SRC}/KOKKOS",
+               LAMMPS_SRC, f"{LAMMPS_SRC}/STUBS", os.path.join(HERE, "..", "include")]
+        cmd = ["/usr/bin/g++", "-std=c++17", "-fsyntax-only", "-DLMP_KOKKOS", "-DLAMMPS_SMALLBIG"] + [f"-I{d}" for d in inc] + \
+              [os.path.join(HERE, "lammps", "pair_ani.cpp")]
+        subprocess.check_call(cmd)
+
+
 TEST_MODEL = os.path.join(HERE, "..", "tools", "test_model")
 
 

@@ -28,7 +28,9 @@
 #include "atom_kokkos.h"
 #include "atom_masks.h"
 #include "kokkos.h"
+#include "memory_kokkos.h"
 #include "neigh_list_kokkos.h"
+#include "neigh_request.h"
 #endif
 
 using namespace LAMMPS_NS;
@@ -408,6 +410,21 @@ void PairANIB200::unpack_reverse_comm(int n, int* idx, double* buf) {
 
 /* ------------------------------------------------------------------------------------------------ ani/kk */
 
+#ifdef LMP_KOKKOS
+/* a Kokkos style as pair_ani_kokkos.cpp:38-46 declares itself: runs in the device execution space, reads x / type, adds to f
+ * (and eatom / vatom there), so that VerletKokkos keeps the DualViews on the device around compute() */
+PairANIB200Device::PairANIB200Device(LAMMPS* lmp) : PairANIB200(lmp) {
+  respa_enable = 0;
+  kokkosable = 1;
+  atomKK = (AtomKokkos*)atom;
+  execution_space = Device;
+  datamask_read = X_MASK | F_MASK | TYPE_MASK | ENERGY_MASK | VIRIAL_MASK;
+  datamask_modify = F_MASK | ENERGY_MASK | VIRIAL_MASK;
+}
+#else
+PairANIB200Device::PairANIB200Device(LAMMPS* lmp) : PairANIB200(lmp) {}
+#endif
+
 void PairANIB200Device::init_style() {
 #ifdef LMP_KOKKOS
   if (!use_fullnbr) error->all(FLERR, "Pair style ANI requires full neighbor list when using kokkos");
@@ -427,8 +444,8 @@ void PairANIB200Device::init_style() {
  * Kokkos keeps them; the table is de-padded on the device only when the list was rebuilt. */
 void PairANIB200Device::compute(int eflag, int vflag) {
   ev_init(eflag, vflag, 0);
-  atomKK->sync(Device, X_MASK | F_MASK | TYPE_MASK);
-  atomKK->modified(Device, F_MASK);
+  atomKK->sync(execution_space, X_MASK | F_MASK | TYPE_MASK);
+  atomKK->modified(execution_space, F_MASK);
   auto x = atomKK->k_x.view<LMPDeviceType>();
   auto f = atomKK->k_f.view<LMPDeviceType>();
   auto type = atomKK->k_type.view<LMPDeviceType>();

@@ -86,7 +86,7 @@ class PairANIB200 : public Pair {
  * device pointers are handed to ani_compute_device directly (pair_ani_kokkos.cpp:67-214). */
 class PairANIB200Device : public PairANIB200 {
  public:
-  PairANIB200Device(class LAMMPS* lmp) : PairANIB200(lmp) {}
+  PairANIB200Device(class LAMMPS* lmp);
   void init_style() override;
 #ifdef LMP_KOKKOS
   void compute(int, int) override;

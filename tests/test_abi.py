@@ -64,3 +64,14 @@ def test_no_cpu_fallback(lib, ani1xnr_path):
         with pytest.raises(RuntimeError):
             ANI(ani1xnr_path, 0)
     lib.ani_model_free(m)
+
+
+def test_kokkos_branch_of_the_pair_style_type_checks():
+    """`ani/kk` on Kokkos views (-DLMP_KOKKOS, reference src/pair_ani_kokkos.cpp:67-235) against the in-tree LAMMPS KOKKOS headers
+    and Kokkos 3.7.01 (Serial backend), g++ -fsyntax-only.  Needs /root/reference (skipped on the GPU box)."""
+    import os
+    import pytest
+    from lammps_ani_b200 import build
+    if not os.path.exists(os.path.join(os.path.dirname(build.LAMMPS_SRC), "lib", "kokkos", "core", "src", "Kokkos_Core.hpp")):
+        pytest.skip("LAMMPS / Kokkos sources not present")
+    build.check_kokkos_branch()
