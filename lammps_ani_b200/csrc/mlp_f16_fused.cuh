@@ -11,17 +11,20 @@
 //   S0  AEV.W1^T  -> h1 = CELU      S1  h1.W2^T -> h2 = CELU       S2  h2.W3^T -> h3, e = <h3,w4>+b4, g3 = w4*CELU'
 //   S3  g3.W3 * CELU'(z2) -> g2     S4  g2.W2 * CELU'(z1) -> g1    S5  g1.W1 -> dE/dAEV (summed over members)
 //
-// The epilogue of stage s writes its output straight into shared memory as 128 x 32 blocks in the K-major SWIZZLE_64B
-// layout of a UMMA A operand (hi + lo plane = 16 KB); stage s+1's MMAs consume a block as soon as it is complete, so the
-// activations never leave the SM.  Only three things touch global memory besides the weights (streamed from L2 through a
+// The epilogue of stage s converts the accumulator IN PLACE in tensor memory: 16 fp32 columns become 8 columns of packed fp16
+// hi values and 8 of lo values (tcgen05.st), which is exactly the K = 16 slice of an A operand held in TMEM, and stage s+1's
+// MMAs (tcgen05.mma with A from TMEM, B = the weights from shared memory) consume each 16-column granule as soon as it is
+// complete -- the activations never leave the SM, never even touch shared memory.  (An earlier version staged them in shared
+// memory: slot hand-offs, proxy fences and st.shared made the per-block chain three times longer.)  Only the last stage's output
+// goes through shared memory, as the source of a TMA store / reduce.  Only three things touch global memory besides the weights (streamed from L2 through a
 // 4 x 32 KB TMA ring) and the AEV tile: CELU'(z1), CELU'(z2) parked in a per-CTA fp32 scratch (written and read back by
 // the SAME thread, so no synchronisation; 224 KB per CTA, L2-resident), the member energies, and the dE/dAEV tile, which
 // is added into the output rows with a TMA reduce (cp.reduce.async.bulk.tensor .add) because the eight members of a row
 // tile are different work items.  Accumulators alternate between TMEM columns 0 and 256.
 //
 // Roles (640 threads): warp 0 TMA producer (weight ring, AEV ring), warp 1 MMA issuer, warp 2 TMEM allocator + TMA
-// store / reduce warp, warp 3 idle, warps 4-19 epilogue: four groups of four warps (one warp per TMEM lane quadrant); group g
-// owns output-block slot g and takes the column blocks cb = g, g+4, ...
+// store / reduce warp, warp 3 idle, warps 4-19 epilogue: warp (q, j) serves TMEM lane quadrant q (rows 32q..32q+31) and the
+// granules gi = j, j+4, ... of every stage.
 // fp16 range guard: every scaled value written to an operand plane is checked against the fp16 maximum; an overflow raises
 // a flag the host turns into an error (nothing silent).
 #pragma once
@@ -37,7 +40,8 @@ constexpr int kFNB = 4;                         // weight ring depth
 constexpr int kFNA = 2;                         // AEV ring depth
 constexpr int kFBSlot = 32768;                  // one weight k-block: 256 rows x 32 halves x (hi + lo)
 constexpr int kFBlk = 16384;                    // 128 rows x 32 halves x (hi + lo), or 128 rows x 32 floats
-constexpr int kFBars = 2 * kFNB + 2 * kFNA + 3 * kFG + 4 + 2;
+constexpr int kFGran = 16;                       // 16-column granules of a stage (N <= 256)
+constexpr int kFBars = 2 * kFNB + 2 * kFNA + 3 * kFG + 4 + 2 + kFGran;
 constexpr float kF16Max = 65504.f;
 // Scale of the activation planes: log2(e) / alpha, so that u = scale * z feeds ex2 directly (e^(z/alpha) = 2^u) and
 // scale * CELU(z) = max(u, c (min(2^u, 1) - 1)) with c = scale * alpha: five instructions per element.  Not a power of two,
@@ -103,6 +107,30 @@ __device__ __forceinline__ void tmem_ld8(uint32_t taddr, uint32_t (&v)[8]) {
   tmem_ld8_nowait(taddr, v);
   asm volatile("tcgen05.wait::ld.sync.aligned;" : "+r"(v[0]), "+r"(v[1]), "+r"(v[2]), "+r"(v[3]), "+r"(v[4]), "+r"(v[5]), "+r"(v[6]), "+r"(v[7])
                :: "memory");
+}
+
+// D[tmem] (+)= A[tmem] . B[smem]: the A operand is read from tensor memory (128 lanes x 8 columns of packed fp16 pairs per K = 16)
+__device__ __forceinline__ void umma_f16_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t db, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "setp.ne.b32 p, %4, 0;\n"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n"
+      "}\n" ::"r"(tmem_d), "r"(tmem_a), "l"(db), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void tmem_st8(uint32_t taddr, const uint32_t (&v)[8]) {
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"r"(taddr), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]),
+               "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]) : "memory");
+}
+__device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ void tmem_ld16w(uint32_t taddr, uint32_t (&v)[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]), "=r"(v[9]),
+        "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+      : "r"(taddr));
+  asm volatile("tcgen05.wait::ld.sync.aligned;" : "+r"(v[0]), "+r"(v[1]), "+r"(v[2]), "+r"(v[3]), "+r"(v[4]), "+r"(v[5]), "+r"(v[6]), "+r"(v[7]),
+               "+r"(v[8]), "+r"(v[9]), "+r"(v[10]), "+r"(v[11]), "+r"(v[12]), "+r"(v[13]), "+r"(v[14]), "+r"(v[15]) :: "memory");
 }
 
 // plain (non-tensor) bulk copy global -> shared, completion on an mbarrier
@@ -181,6 +209,7 @@ f16_fused_kernel(const __grid_constant__ FusedMaps maps, const __grid_constant__
   // (parity waits alias two phases apart), and the store warp sees only those blocks, the MMA issuer only the others
   auto dfull = [&](int i) { return bar_base + 8u * (uint32_t)(2 * kFNB + 2 * kFNA + 2 * kFG + 4 + i); };
   auto cfull = [&](int i) { return bar_base + 8u * (uint32_t)(2 * kFNB + 2 * kFNA + 3 * kFG + 4 + i); };
+  auto gfull = [&](int i) { return bar_base + 8u * (uint32_t)(2 * kFNB + 2 * kFNA + 3 * kFG + 4 + 2 + i); };   // granule i of the current stage converted
   const uint32_t tmem_slot = bar_base + 8u * (uint32_t)kFBars;
   volatile uint32_t* tmem_slot_ptr = (volatile uint32_t*)(smem_raw + (tmem_slot - raw));
 
@@ -192,8 +221,10 @@ f16_fused_kernel(const __grid_constant__ FusedMaps maps, const __grid_constant__
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < kFNB; i++) { mbar_init(bfull(i), 1); mbar_init(bempty(i), 1); }
     for (int i = 0; i < kFNA; i++) { mbar_init(afull(i), 1); mbar_init(aempty(i), 1); }
-    for (int i = 0; i < kFG; i++) { mbar_init(hfull(i), 4 * kFG); mbar_init(hfree(i), 1); mbar_init(dfull(i), 4 * kFG); }
+    // an output block is announced by the warps that wrote it: all sixteen for an fp32 dE/dAEV block, eight for a g1 block
+    for (int i = 0; i < kFG; i++) { mbar_init(hfull(i), 1); mbar_init(hfree(i), 1); mbar_init(dfull(i), g.nstages == kFusedMaxStages ? 4 * kFG : 8); }
     for (int i = 0; i < 2; i++) { mbar_init(accfull(i), 1); mbar_init(accfree(i), 4 * kFG); mbar_init(cfull(i), 1); }
+    for (int i = 0; i < kFGran; i++) mbar_init(gfull(i), 4);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 2) {
@@ -240,10 +271,7 @@ f16_fused_kernel(const __grid_constant__ FusedMaps maps, const __grid_constant__
   } else if (warp == 1) {
     // ================================================================= MMA issuer (warp-uniform loop, one elected lane issues)
     {
-      uint32_t bq = 0, aq = 0, t = 0;
-      uint32_t hbase[kFG];
-#pragma unroll
-      for (int i = 0; i < kFG; i++) hbase[i] = 0;
+      uint32_t bq = 0, aq = 0, t = 0, gpar = 0;     // gpar bit i: parity of the uses of granule barrier i so far
       long long w_acc = 0, w_b = 0, w_a = 0, w_i = 0, t_begin = 0;
       if (PROF) t_begin = clock64();
       // weight k-blocks this CTA consumes in total: the wait for the NEXT one is taken off the critical path (it is issued right
@@ -281,39 +309,55 @@ f16_fused_kernel(const __grid_constant__ FusedMaps maps, const __grid_constant__
           const uint32_t idesc = umma_idesc_f16(BM, g.N[s]);
           const int K = g.K[s], KB = (K + 31) / 32;
           const uint32_t bplane = (uint32_t)g.N[s] * 64u;
+          const uint32_t tmem_a0 = tmem_base + (r ^ 1u) * 256u;      // stage s-1's accumulator, converted in place (s >= 1)
           for (int kb = 0; kb < KB; kb++) {
             const int sb = (int)(bq % (uint32_t)kFNB);      // (its weights were waited for one k-block ago)
             if (PROF) c0 = clock64();
-            uint32_t sA;
-            int sa;
-            if (s == 0) {
-              sa = (int)(aq % (uint32_t)kFNA);
-              mbar_wait_wd(afull(sa), (aq / (uint32_t)kFNA) & 1u, g.dbg, WD(2, sa));
-              sA = baseA + (uint32_t)sa * kFBlk;
-            } else {
-              sa = kb % kFG;
-              mbar_wait_wd(hfull(sa), (hbase[sa] + (uint32_t)(kb / kFG)) & 1u, g.dbg, WD(4, sa));
-              sA = baseH + (uint32_t)sa * kFBlk;
-            }
-            if (PROF) { const long long c1 = clock64(); w_a += c1 - c0; c0 = c1; }
-            tc_fence_after();
             const uint32_t sB = baseB + (uint32_t)sb * kFBSlot;
-            const uint64_t dA_hi = umma_desc_k(sA, 32), dA_lo = umma_desc_k(sA + kFBlk / 2, 32);
             const uint64_t dB_hi = umma_desc_k(sB, 32), dB_lo = umma_desc_k(sB + bplane, 32);
             const int nks = min(2, (K - kb * 32) / 16);
-            if (elect_one()) {
-              for (int k = 0; k < nks; k++) {
-                const uint64_t adv = (uint64_t)(2 * k);          // 16 halves = 32 bytes along K, in 16-byte units
-                umma_f16(tmem_d, dA_hi + adv, dB_hi + adv, idesc, (kb | k) != 0 ? 1u : 0u);
-                umma_f16(tmem_d, dA_lo + adv, dB_hi + adv, idesc, 1u);
-                umma_f16(tmem_d, dA_hi + adv, dB_lo + adv, idesc, 1u);
+            if (s == 0) {
+              // A = the AEV tile from shared memory (TMA)
+              const int sa = (int)(aq % (uint32_t)kFNA);
+              mbar_wait_wd(afull(sa), (aq / (uint32_t)kFNA) & 1u, g.dbg, WD(2, sa));
+              if (PROF) { const long long c1 = clock64(); w_a += c1 - c0; c0 = c1; }
+              tc_fence_after();
+              const uint32_t sA = baseA + (uint32_t)sa * kFBlk;
+              const uint64_t dA_hi = umma_desc_k(sA, 32), dA_lo = umma_desc_k(sA + kFBlk / 2, 32);
+              if (elect_one()) {
+                for (int k = 0; k < nks; k++) {
+                  const uint64_t adv = (uint64_t)(2 * k);          // 16 halves = 32 bytes along K, in 16-byte units
+                  umma_f16(tmem_d, dA_hi + adv, dB_hi + adv, idesc, (kb | k) != 0 ? 1u : 0u);
+                  umma_f16(tmem_d, dA_lo + adv, dB_hi + adv, idesc, 1u);
+                  umma_f16(tmem_d, dA_hi + adv, dB_lo + adv, idesc, 1u);
+                }
+                umma_commit(bempty(sb));
+                umma_commit(aempty(sa));
               }
-              umma_commit(bempty(sb));
-              umma_commit(s == 0 ? aempty(sa) : hfree(sa));
+              __syncwarp();
+              aq++;
+            } else {
+              // A = granules 2 kb, 2 kb + 1 of the previous stage, fp16 hi / lo pairs in tensor memory
+              for (int k = 0; k < nks; k++) {
+                const int gi = 2 * kb + k;
+                mbar_wait_wd(gfull(gi), (gpar >> gi) & 1u, g.dbg, WD(4, gi));
+                gpar ^= 1u << gi;
+                if (PROF) { const long long c1 = clock64(); w_a += c1 - c0; c0 = c1; }
+                tc_fence_after();
+                if (elect_one()) {
+                  const uint32_t ta = tmem_a0 + (uint32_t)(16 * gi);
+                  const uint64_t adv = (uint64_t)(2 * k);
+                  umma_f16_ts(tmem_d, ta, dB_hi + adv, idesc, (kb | k) != 0 ? 1u : 0u);
+                  umma_f16_ts(tmem_d, ta + 8u, dB_hi + adv, idesc, 1u);
+                  umma_f16_ts(tmem_d, ta, dB_lo + adv, idesc, 1u);
+                }
+                __syncwarp();
+                if (PROF) { const long long c1 = clock64(); w_i += c1 - c0; c0 = c1; }
+              }
+              if (elect_one()) umma_commit(bempty(sb));
+              __syncwarp();
             }
-            __syncwarp();
             bq++;
-            if (s == 0) aq++;
             if (PROF) { const long long c1 = clock64(); w_i += c1 - c0; c0 = c1; }
             if (bq < total_kb) {
               const int sn = (int)(bq % (uint32_t)kFNB);
@@ -323,11 +367,6 @@ f16_fused_kernel(const __grid_constant__ FusedMaps maps, const __grid_constant__
           }
           if (elect_one()) umma_commit(accfull(r));
           __syncwarp();
-          if (s > 0) {
-            const int nbp = g.N[s - 1] >> 5;
-#pragma unroll
-            for (int i = 0; i < kFG; i++) hbase[i] += (uint32_t)fused_uses(nbp, i);
-          }
         }
       }                                           // (the last stage's blocks go to the store warp, on dfull)
       if (PROF && g.prof && lane == 0) {
@@ -365,23 +404,23 @@ f16_fused_kernel(const __grid_constant__ FusedMaps maps, const __grid_constant__
     }
   } else if (warp >= 4) {
     // ================================================================= epilogue warps
-    // Every 128 x 32 output block is produced by ALL sixteen warps: warp (quadrant q, slice j) converts columns 8j..8j+7 of
-    // rows 32q..32q+31, one 16-byte chunk per plane.  Blocks therefore complete one after the other, a quarter of a "round"
-    // apart, and the next stage's MMAs follow one block behind (with one warp group per block, four blocks used to land at
-    // the same moment: the tensor pipe idled for a whole round at every stage boundary).  TMEM slices and CELU' vectors are
-    // fetched one block ahead.
-    const int q = warp & 3, j8 = (warp - 4) >> 2;                 // lane quadrant, 8-column slice inside a block
+    // Warp (q, j) owns TMEM lanes 32q..32q+31 and the 16-column granules gi = j, j+4, ... of every stage.  A granule of the
+    // accumulator is read (tcgen05.ld), turned into the next stage's operand (bias + CELU / * CELU', fp16 hi + lo split) and
+    // written back over itself (tcgen05.st: 8 columns hi, 8 columns lo); the MMA warp is told per granule.  The four warps of a
+    // quadrant work on four different granules at once, so granules complete in bursts of four, 64 columns = two weight
+    // k-blocks, and the next stage's MMAs trail by at most that.
+    const int q = warp & 3, j8 = (warp - 4) >> 2;                 // lane quadrant, granule phase (and 8-column slice in S5)
     const int r = q * 32 + lane;                                  // row inside the 128-row tile
     float4* const scr = (float4*)(g.scratch + (size_t)blockIdx.x * g.scratch_per_cta);
     const int n1 = g.N[0];
-    uint32_t hpar = 0, t = 0, cuse[2] = {0, 0};                   // hpar bit i: parity of the uses of output-block slot i so far
+    uint32_t hpar = 0, t = 0, cuse[2] = {0, 0};                   // hpar bit i: parity of this warp's uses of output-block slot i
     long long w_acc = 0, w_h = 0, t_begin = 0;
     const bool prof_me = PROF && warp == 4 && lane == 0;
     if (prof_me) t_begin = clock64();
-    // float4 index of (block cb, quadrant q, vector 2*j8, lane) in a CELU' scratch area; a warp's store / load of one vector is
-    // 512 contiguous bytes
-    auto dvec0 = [&](int cb) { return ((cb * 4 + q) * 8 + 2 * j8) * 32 + lane; };
-    const uint32_t lane_taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(8 * j8);
+    // float4 index of (granule gi, quadrant q, vector 0, lane) in a CELU' scratch area (vector v is 32 float4 further on): a
+    // warp's store / load of one vector is 512 contiguous bytes, and a value is read back by the thread that wrote it
+    auto dgran0 = [&](int gi) { return ((gi * 4 + q) * 4) * 32 + lane; };
+    const uint32_t quad_taddr = tmem_base + ((uint32_t)(q * 32) << 16);
 
     for (int it = blockIdx.x; it < num_items; it += gridDim.x) {
       const int rt = it / g.batch, z = it % g.batch;
@@ -401,17 +440,12 @@ f16_fused_kernel(const __grid_constant__ FusedMaps maps, const __grid_constant__
         cuse[rr]++;
         return baseC + rr * (uint32_t)g.cslot_bytes;
       };
-      auto wait_slot = [&](int slot) {           // the previous block in this slot has been consumed
+      auto wait_slot = [&](int slot) {           // the previous block in this output slot has left (TMA store / reduce read it)
         long long c0 = 0;
         if (prof_me) c0 = clock64();
         mbar_wait_wd(hfree(slot), ((hpar >> slot) & 1u) ^ 1u, g.dbg, WD(5, slot));
         hpar ^= 1u << slot;
         if (prof_me) w_h += clock64() - c0;
-      };
-      auto publish = [&](int slot, bool last_stage) {
-        fence_async_smem();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(last_stage ? dfull(slot) : hfull(slot));
       };
       auto end_stage = [&]() {
         tc_fence_before();
@@ -419,118 +453,151 @@ f16_fused_kernel(const __grid_constant__ FusedMaps maps, const __grid_constant__
         if (lane == 0) mbar_arrive(accfree(t & 1u));
         t++;
       };
-      auto tslice = [&](int cb) { return lane_taddr + (t & 1u) * 256u + (uint32_t)(cb * 32); };
-      // hi / lo planes of 8 values -> chunk j8 of row r in block slot `slot`
-      auto put8 = [&](int slot, const float (&x)[8]) {
-        uint32_t hh[4], ll[4];
+      auto gaddr = [&](int gi) { return quad_taddr + (t & 1u) * 256u + (uint32_t)(16 * gi); };
+      // 16 values -> fp16 hi / lo pairs -> back over the granule they came from; tell the MMA warp
+      auto emit_tmem = [&](int gi, const float (&x)[16]) {
+        uint32_t hh[8], ll[8];
 #pragma unroll
-        for (int e = 0; e < 4; e++) {
+        for (int e = 0; e < 8; e++) {
           amax = fmaxf(fmaxf(fabsf(x[2 * e]), fabsf(x[2 * e + 1])), amax);
           split2(x[2 * e], x[2 * e + 1], hh[e], ll[e]);
         }
-        const uint32_t dst = baseH + (uint32_t)slot * kFBlk + blk_off64(r, j8);
-        sts128(dst, hh[0], hh[1], hh[2], hh[3]);
-        sts128(dst + kFBlk / 2, ll[0], ll[1], ll[2], ll[3]);
+        const uint32_t ta = gaddr(gi);
+        tmem_st8(ta, hh);
+        tmem_st8(ta + 8u, ll);
+        tmem_st_wait();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(gfull(gi));
+      };
+      // the same 16 values into an output block in shared memory (the K-major SWIZZLE_64B layout of the g1 planes' TMA store);
+      // granules 2 cb and 2 cb + 1 make block cb
+      auto emit_smem = [&](int gi, const float (&x)[16]) {
+        const int slot = (gi >> 1) & (kFG - 1);
+        wait_slot(slot);
+        const uint32_t dstb = baseH + (uint32_t)slot * kFBlk;
+#pragma unroll
+        for (int hchunk = 0; hchunk < 2; hchunk++) {
+          uint32_t hh[4], ll[4];
+#pragma unroll
+          for (int e = 0; e < 4; e++) {
+            const float x0 = x[hchunk * 8 + 2 * e], x1 = x[hchunk * 8 + 2 * e + 1];
+            amax = fmaxf(fmaxf(fabsf(x0), fabsf(x1)), amax);
+            split2(x0, x1, hh[e], ll[e]);
+          }
+          const uint32_t off = blk_off64(r, 2 * (gi & 1) + hchunk);
+          sts128(dstb + off, hh[0], hh[1], hh[2], hh[3]);
+          sts128(dstb + kFBlk / 2 + off, ll[0], ll[1], ll[2], ll[3]);
+        }
+        fence_async_smem();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(dfull(slot));
       };
 
-      // ---------------- S0, S1: u = kFScaleH * z = acc*a + b';  h = CELU -> planes (x kFScaleH);  CELU'(z) -> scratch
+      // ---------------- S0, S1: u = kFScaleH * z = acc*a + b';  h = CELU -> operand (x kFScaleH);  CELU'(z) -> scratch
 #pragma unroll 1
       for (int s = 0; s < 2; s++) {
-        const int nb = g.N[s] >> 5;
+        const int ng = g.N[s] >> 4;
         const float a = kFScaleH * g.acc_scale[s];
         float4* const dst = scr + (s == 0 ? 0 : n1 * 32);       // n1*128 floats = n1*32 float4
         wait_acc();
-        const uint32_t cb_s = wait_consts() + (uint32_t)j8 * 32u;
-        uint32_t v[8], vn[8];
-        tmem_ld8(tslice(0), v);
+        const uint32_t cb_s = wait_consts();
 #pragma unroll 1
-        for (int cb = 0; cb < nb; cb++) {
-          const int slot = cb & (kFG - 1);
-          if (cb + 1 < nb) tmem_ld8_nowait(tslice(cb + 1), vn);
-          const float4 b0 = lds_f4(cb_s + (uint32_t)cb * 128u), b1 = lds_f4(cb_s + (uint32_t)cb * 128u + 16u);
-          const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
-          float h[8], d[8];
+        for (int gi = j8; gi < ng; gi += 4) {
+          uint32_t v[16];
+          tmem_ld16w(gaddr(gi), v);
+          float h[16];
+          float4* const dp = dst + dgran0(gi);
 #pragma unroll
-          for (int e = 0; e < 8; e++) {
-            const float u = fmaf(__uint_as_float(v[e]), a, bb[e]);            // log2(e)/alpha * z
-            d[e] = fminf(exp2f(u), 1.f);                                      // CELU'(z) = min(e^(z/alpha), 1)
-            h[e] = fmaxf(u, fmaf(kFCeluC, d[e], -kFCeluC));                   // kFScaleH * CELU(z)   (e^x - 1 >= x)
+          for (int c4 = 0; c4 < 4; c4++) {
+            const float4 bq = lds_f4(cb_s + (uint32_t)gi * 64u + c4 * 16u);
+            const float bb[4] = {bq.x, bq.y, bq.z, bq.w};
+            float d[4];
+#pragma unroll
+            for (int e = 0; e < 4; e++) {
+              const float u = fmaf(__uint_as_float(v[c4 * 4 + e]), a, bb[e]);   // log2(e)/alpha * z
+              d[e] = fminf(exp2f(u), 1.f);                                      // CELU'(z) = min(e^(z/alpha), 1)
+              h[c4 * 4 + e] = fmaxf(u, fmaf(kFCeluC, d[e], -kFCeluC));          // kFScaleH * CELU(z)   (e^x - 1 >= x)
+            }
+            __stcg(dp + c4 * 32, make_float4(d[0], d[1], d[2], d[3]));
           }
-          float4* const dp = dst + dvec0(cb);
-          __stcg(dp, make_float4(d[0], d[1], d[2], d[3]));
-          __stcg(dp + 32, make_float4(d[4], d[5], d[6], d[7]));
-          wait_slot(slot);
-          put8(slot, h);
-          publish(slot, false);
-          if (cb + 1 < nb) tmem_ld_wait8(vn, v);
+          emit_tmem(gi, h);
         }
         end_stage();
       }
-      // ---------------- S2: h3 = CELU(z3); e += <h3, w4>; g3 = w4 * CELU'(z3) -> planes (x kScaleG)
+      // ---------------- S2: h3 = CELU(z3); e += <h3, w4>; g3 = w4 * CELU'(z3) -> operand (x kScaleG)
       {
-        const int nb = g.N[2] >> 5;
+        const int ng = g.N[2] >> 4;
         const float a = kFScaleH * g.acc_scale[2];
         wait_acc();
-        const uint32_t cb_s = wait_consts() + (uint32_t)j8 * 32u;
+        const uint32_t cb_s = wait_consts();
         const uint32_t w_s = cb_s + (uint32_t)g.N[2] * 4u;
-        uint32_t v[8], vn[8];
-        tmem_ld8(tslice(0), v);
 #pragma unroll 1
-        for (int cb = 0; cb < nb; cb++) {
-          const int slot = cb & (kFG - 1);
-          if (cb + 1 < nb) tmem_ld8_nowait(tslice(cb + 1), vn);
-          const float4 b0 = lds_f4(cb_s + (uint32_t)cb * 128u), b1 = lds_f4(cb_s + (uint32_t)cb * 128u + 16u);
-          const float4 w0 = lds_f4(w_s + (uint32_t)cb * 128u), w1 = lds_f4(w_s + (uint32_t)cb * 128u + 16u);
-          const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
-          const float ww[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
-          float gg[8];
+        for (int gi = j8; gi < ng; gi += 4) {
+          uint32_t v[16];
+          tmem_ld16w(gaddr(gi), v);
+          float gg[16];
 #pragma unroll
-          for (int e = 0; e < 8; e++) {
-            const float u = fmaf(__uint_as_float(v[e]), a, bb[e]);
-            const float d = fminf(exp2f(u), 1.f);
-            const float h = fmaxf(u, fmaf(kFCeluC, d, -kFCeluC));
-            e_acc = fmaf(h, ww[e], e_acc);                      // x kFScaleH * kScaleG, folded back below
-            gg[e] = ww[e] * d;
+          for (int c4 = 0; c4 < 4; c4++) {
+            const float4 bq = lds_f4(cb_s + (uint32_t)gi * 64u + c4 * 16u), wq = lds_f4(w_s + (uint32_t)gi * 64u + c4 * 16u);
+            const float bb[4] = {bq.x, bq.y, bq.z, bq.w}, ww[4] = {wq.x, wq.y, wq.z, wq.w};
+#pragma unroll
+            for (int e = 0; e < 4; e++) {
+              const float u = fmaf(__uint_as_float(v[c4 * 4 + e]), a, bb[e]);
+              const float d = fminf(exp2f(u), 1.f);
+              const float h = fmaxf(u, fmaf(kFCeluC, d, -kFCeluC));
+              e_acc = fmaf(h, ww[e], e_acc);                    // x kFScaleH * kScaleG, folded back below
+              gg[c4 * 4 + e] = ww[e] * d;
+            }
           }
-          wait_slot(slot);
-          put8(slot, gg);
-          publish(slot, false);
-          if (cb + 1 < nb) tmem_ld_wait8(vn, v);
+          emit_tmem(gi, gg);
         }
         end_stage();
-        if (row < g.R)                                          // e_out is zeroed before the launch; the column slices add their parts
+        if (row < g.R)                                          // e_out is zeroed before the launch; the warps of a row add their parts
           atomicAdd(g.e_out + (size_t)row * g.e_ld + z, e_acc * (1.0f / (kFScaleH * kScaleG)) + (j8 == 0 ? __ldg(g.b_out + z) : 0.f));
       }
-      // ---------------- S3, S4: g = acc * s * CELU'(z) (from scratch) -> planes
+      // ---------------- S3, S4: g = acc * s * CELU'(z) (from scratch) -> operand; S4's output leaves through shared memory when the
+      // dE/dAEV GEMM is not fused (ns == 5)
 #pragma unroll 1
       for (int s = 3; s < 5; s++) {
-        const int nb = g.N[s] >> 5;
+        const int ng = g.N[s] >> 4;
         const float a = g.acc_scale[s];
         const float4* const src = scr + (s == 3 ? n1 * 32 : 0);
-        float4 d0 = __ldcg(src + dvec0(0)), d1 = __ldcg(src + dvec0(0) + 32);   // the first block's CELU' does not need the accumulator
-        wait_acc();
-        uint32_t v[8], vn[8];
-        tmem_ld8(tslice(0), v);
-#pragma unroll 1
-        for (int cb = 0; cb < nb; cb++) {
-          const int slot = cb & (kFG - 1);
-          float4 d0n = d0, d1n = d1;
-          if (cb + 1 < nb) {
-            tmem_ld8_nowait(tslice(cb + 1), vn);
-            d0n = __ldcg(src + dvec0(cb + 1)); d1n = __ldcg(src + dvec0(cb + 1) + 32);
-          }
-          const float d8[8] = {d0.x, d0.y, d0.z, d0.w, d1.x, d1.y, d1.z, d1.w};
-          float gg[8];
+        const bool to_smem = (s == ns - 1);
+        float4 dd[4];
+        if (j8 < ng) {                                          // the first granule's CELU' does not need the accumulator
+          const float4* const dp = src + dgran0(j8);
 #pragma unroll
-          for (int e = 0; e < 8; e++) gg[e] = __uint_as_float(v[e]) * a * d8[e];
-          wait_slot(slot);
-          put8(slot, gg);
-          publish(slot, s == ns - 1);
-          if (cb + 1 < nb) tmem_ld_wait8(vn, v);
-          d0 = d0n; d1 = d1n;
+          for (int c4 = 0; c4 < 4; c4++) dd[c4] = __ldcg(dp + c4 * 32);
+        }
+        wait_acc();
+#pragma unroll 1
+        for (int gi = j8; gi < ng; gi += 4) {
+          uint32_t v[16];
+          tmem_ld16w(gaddr(gi), v);
+          float gg[16];
+#pragma unroll
+          for (int c4 = 0; c4 < 4; c4++) {
+            const float d4[4] = {dd[c4].x, dd[c4].y, dd[c4].z, dd[c4].w};
+#pragma unroll
+            for (int e = 0; e < 4; e++) gg[c4 * 4 + e] = __uint_as_float(v[c4 * 4 + e]) * a * d4[e];
+          }
+          if (gi + 4 < ng) {                                    // next granule's CELU' while this one is written back
+            const float4* const dp = src + dgran0(gi + 4);
+#pragma unroll
+            for (int c4 = 0; c4 < 4; c4++) dd[c4] = __ldcg(dp + c4 * 32);
+          }
+          if (to_smem) emit_smem(gi, gg); else emit_tmem(gi, gg);
         }
         end_stage();
       }
+      // 8-column slices of a 32-column block for S5 (all sixteen warps on one fp32 output block)
+      auto tslice = [&](int cb) { return quad_taddr + (uint32_t)(8 * j8) + (t & 1u) * 256u + (uint32_t)(cb * 32); };
+      auto publish = [&](int slot, bool) {
+        fence_async_smem();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(dfull(slot));
+      };
       // ---------------- S5: dE/dAEV tile of this member -> fp32 block (SWIZZLE_128B) -> TMA reduce-add
       if (ns == kFusedMaxStages) {
         const int nb = g.N[5] >> 5;
