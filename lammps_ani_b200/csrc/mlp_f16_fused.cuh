@@ -63,7 +63,8 @@ struct FusedArgs {
   int g1_col_off_per_z;
   int* flag;                                    // |= 1 when a plane value left the fp16 range
   int* dbg;                                     // host-mapped words of the wait watchdog
-  long long* prof;                              // optional cycle counters, 8 per CTA
+  long long* prof;                              // optional cycle counters, 8 per CTA, then 64 trace stamps of CTA 0's third item
+  int prof_ctas;
 };
 
 struct alignas(64) FusedMaps {
@@ -209,7 +210,7 @@ f16_fused_kernel(const __grid_constant__ FusedMaps maps, const __grid_constant__
   // (parity waits alias two phases apart), and the store warp sees only those blocks, the MMA issuer only the others
   auto dfull = [&](int i) { return bar_base + 8u * (uint32_t)(2 * kFNB + 2 * kFNA + 2 * kFG + 4 + i); };
   auto cfull = [&](int i) { return bar_base + 8u * (uint32_t)(2 * kFNB + 2 * kFNA + 3 * kFG + 4 + i); };
-  auto gfull = [&](int i) { return bar_base + 8u * (uint32_t)(2 * kFNB + 2 * kFNA + 3 * kFG + 4 + 2 + i); };   // granule i of the current stage converted
+  auto gfull = [&](int i) { return bar_base + 8u * (uint32_t)(2 * kFNB + 2 * kFNA + 3 * kFG + 4 + 2 + i); };   // granules 2i, 2i+1 of the current stage converted
   const uint32_t tmem_slot = bar_base + 8u * (uint32_t)kFBars;
   volatile uint32_t* tmem_slot_ptr = (volatile uint32_t*)(smem_raw + (tmem_slot - raw));
 
@@ -224,7 +225,7 @@ f16_fused_kernel(const __grid_constant__ FusedMaps maps, const __grid_constant__
     // an output block is announced by the warps that wrote it: all sixteen for an fp32 dE/dAEV block, eight for a g1 block
     for (int i = 0; i < kFG; i++) { mbar_init(hfull(i), 1); mbar_init(hfree(i), 1); mbar_init(dfull(i), g.nstages == kFusedMaxStages ? 4 * kFG : 8); }
     for (int i = 0; i < 2; i++) { mbar_init(accfull(i), 1); mbar_init(accfree(i), 4 * kFG); mbar_init(cfull(i), 1); }
-    for (int i = 0; i < kFGran; i++) mbar_init(gfull(i), 4);
+    for (int i = 0; i < kFGran; i++) mbar_init(gfull(i), 8);       // a pair of granules: two warps of each quadrant
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 2) {
@@ -310,6 +311,9 @@ f16_fused_kernel(const __grid_constant__ FusedMaps maps, const __grid_constant__
           const int K = g.K[s], KB = (K + 31) / 32;
           const uint32_t bplane = (uint32_t)g.N[s] * 64u;
           const uint32_t tmem_a0 = tmem_base + (r ^ 1u) * 256u;      // stage s-1's accumulator, converted in place (s >= 1)
+          const bool tr = PROF && g.prof && blockIdx.x == 0 && it == (int)(2 * gridDim.x) && lane == 0;
+          long long* const trp = g.prof + (size_t)g.prof_ctas * 8 + s * 8;
+          if (tr) trp[0] = clock64();                                 // stage start: TMEM region free
           for (int kb = 0; kb < KB; kb++) {
             const int sb = (int)(bq % (uint32_t)kFNB);      // (its weights were waited for one k-block ago)
             if (PROF) c0 = clock64();
@@ -337,24 +341,24 @@ f16_fused_kernel(const __grid_constant__ FusedMaps maps, const __grid_constant__
               __syncwarp();
               aq++;
             } else {
-              // A = granules 2 kb, 2 kb + 1 of the previous stage, fp16 hi / lo pairs in tensor memory
-              for (int k = 0; k < nks; k++) {
-                const int gi = 2 * kb + k;
-                mbar_wait_wd(gfull(gi), (gpar >> gi) & 1u, g.dbg, WD(4, gi));
-                gpar ^= 1u << gi;
-                if (PROF) { const long long c1 = clock64(); w_a += c1 - c0; c0 = c1; }
-                tc_fence_after();
-                if (elect_one()) {
-                  const uint32_t ta = tmem_a0 + (uint32_t)(16 * gi);
-                  const uint64_t adv = (uint64_t)(2 * k);
-                  umma_f16_ts(tmem_d, ta, dB_hi + adv, idesc, (kb | k) != 0 ? 1u : 0u);
-                  umma_f16_ts(tmem_d, ta + 8u, dB_hi + adv, idesc, 1u);
-                  umma_f16_ts(tmem_d, ta, dB_lo + adv, idesc, 1u);
-                }
-                __syncwarp();
-                if (PROF) { const long long c1 = clock64(); w_i += c1 - c0; c0 = c1; }
+              // A = granules 2 kb, 2 kb + 1 of the previous stage, fp16 hi / lo pairs in tensor memory; one barrier per pair
+              // (the two granules belong to neighbouring warps of each quadrant and land together)
+              mbar_wait_wd(gfull(kb), (gpar >> kb) & 1u, g.dbg, WD(4, kb));
+              gpar ^= 1u << kb;
+              if (tr && kb == 0) trp[1] = clock64();                  // first granule pair there
+              if (tr && kb == KB - 1) trp[2] = clock64();             // last granule pair there
+              if (PROF) { const long long c1 = clock64(); w_a += c1 - c0; c0 = c1; }
+              tc_fence_after();
+              if (elect_one()) {
+                const uint32_t ta = tmem_a0 + (uint32_t)(32 * kb);
+                umma_f16_ts(tmem_d, ta, dB_hi, idesc, kb != 0 ? 1u : 0u);
+                umma_f16_ts(tmem_d, ta + 8u, dB_hi, idesc, 1u);
+                umma_f16_ts(tmem_d, ta, dB_lo, idesc, 1u);
+                umma_f16_ts(tmem_d, ta + 16u, dB_hi + 2u, idesc, 1u);
+                umma_f16_ts(tmem_d, ta + 24u, dB_hi + 2u, idesc, 1u);
+                umma_f16_ts(tmem_d, ta + 16u, dB_lo + 2u, idesc, 1u);
+                umma_commit(bempty(sb));
               }
-              if (elect_one()) umma_commit(bempty(sb));
               __syncwarp();
             }
             bq++;
@@ -365,6 +369,7 @@ f16_fused_kernel(const __grid_constant__ FusedMaps maps, const __grid_constant__
             }
             if (PROF) w_b += clock64() - c0;
           }
+          if (tr) trp[3] = clock64();                                 // all MMAs of the stage issued
           if (elect_one()) umma_commit(accfull(r));
           __syncwarp();
         }
@@ -427,12 +432,16 @@ f16_fused_kernel(const __grid_constant__ FusedMaps maps, const __grid_constant__
       const int row = rt * BM + r;
       float amax = 0.f, e_acc = 0.f;
 
+      const bool etr = prof_me && g.prof && blockIdx.x == 0 && it == (int)(2 * gridDim.x);
+      int estage = 0;
       auto wait_acc = [&]() {
         long long c0 = 0;
         if (prof_me) c0 = clock64();
         mbar_wait_wd(accfull(t & 1u), (t >> 1) & 1u, g.dbg, WD(8, t & 1u));
         if (prof_me) w_acc += clock64() - c0;
         tc_fence_after();
+        if (etr) g.prof[(size_t)g.prof_ctas * 8 + estage * 8 + 4] = clock64();     // accumulator seen complete
+        estage++;
       };
       auto wait_consts = [&]() {                 // returns the shared-memory address of this stage's constants
         const uint32_t rr = t & 1u;
@@ -448,6 +457,7 @@ f16_fused_kernel(const __grid_constant__ FusedMaps maps, const __grid_constant__
         if (prof_me) w_h += clock64() - c0;
       };
       auto end_stage = [&]() {
+        if (etr) g.prof[(size_t)g.prof_ctas * 8 + (estage - 1) * 8 + 6] = clock64();   // this warp's last granule of the stage written
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(accfree(t & 1u));
@@ -468,7 +478,8 @@ f16_fused_kernel(const __grid_constant__ FusedMaps maps, const __grid_constant__
         tmem_st_wait();
         tc_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive(gfull(gi));
+        if (lane == 0) mbar_arrive(gfull(gi >> 1));
+        if (etr && gi == j8) g.prof[(size_t)g.prof_ctas * 8 + (estage - 1) * 8 + 5] = clock64();   // this warp's first granule written
       };
       // the same 16 values into an output block in shared memory (the K-major SWIZZLE_64B layout of the g1 planes' TMA store);
       // granules 2 cb and 2 cb + 1 make block cb
@@ -692,7 +703,7 @@ inline int mlp_species_fused(cudaStream_t st, SpeciesWeights& w, FusedWork& work
   const int ctas = opt.cta_cap > 0 ? std::min(num_sms, opt.cta_cap) : num_sms;
   const long long scratch_per_cta = (long long)(n1 + n2) * BM;
   if (!work.scratch.reserve((size_t)ctas * scratch_per_cta * 4) || !work.e.reserve((size_t)std::max(R, 1) * M * 4) ||
-      (opt.prof && !work.prof.reserve((size_t)ctas * 8 * sizeof(long long))) ||
+      (opt.prof && !work.prof.reserve((size_t)(ctas * 8 + 64) * sizeof(long long))) ||
       (!fuse_d && !work.G1.reserve((size_t)std::min(chunk, (R + BM - 1) / BM * BM) * M * n1))) {
     set_error("out of memory for MLP work buffers");
     return 1;
@@ -724,6 +735,7 @@ inline int mlp_species_fused(cudaStream_t st, SpeciesWeights& w, FusedWork& work
     g.flag = opt.flag;
     g.dbg = fused_dbg_word(true);
     g.prof = opt.prof ? (long long*)work.prof.p : nullptr;
+    g.prof_ctas = ctas;
     if (make_operand_map(&mp.a_hi, aev_hi, (uint64_t)aev_rows_total, (uint64_t)Lin, (uint64_t)ld_aev, BM, 32) ||
         make_operand_map(&mp.a_lo, aev_lo, (uint64_t)aev_rows_total, (uint64_t)Lin, (uint64_t)ld_aev, BM, 32) ||
         weight_map(&mp.b_hi[0], &mp.b_lo[0], w.Wf[0], (uint64_t)M * n1, (uint64_t)Lin, (uint32_t)n1) ||
@@ -746,7 +758,7 @@ inline int mlp_species_fused(cudaStream_t st, SpeciesWeights& w, FusedWork& work
     const int grid = std::max(1, std::min(items, ctas));
     if (opt.prof) {
       ANIB_CUDA_OK(cudaFuncSetAttribute(f16_fused_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-      ANIB_CUDA_OK(cudaMemsetAsync(work.prof.p, 0, (size_t)ctas * 8 * sizeof(long long), st));
+      ANIB_CUDA_OK(cudaMemsetAsync(work.prof.p, 0, (size_t)(ctas * 8 + 64) * sizeof(long long), st));
       f16_fused_kernel<true><<<grid, kFThreads, smem, st>>>(mp, g);
     } else {
       ANIB_CUDA_OK(cudaFuncSetAttribute(f16_fused_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
@@ -755,9 +767,17 @@ inline int mlp_species_fused(cudaStream_t st, SpeciesWeights& w, FusedWork& work
     ANIB_CUDA_OK(cudaGetLastError());
     if (launches) (*launches)++;
     if (opt.prof) {
-      std::vector<long long> h((size_t)grid * 8);
+      std::vector<long long> h((size_t)grid * 8), tr(64);
       ANIB_CUDA_OK(cudaStreamSynchronize(st));
       ANIB_CUDA_OK(cudaMemcpy(h.data(), work.prof.p, h.size() * sizeof(long long), cudaMemcpyDeviceToHost));
+      ANIB_CUDA_OK(cudaMemcpy(tr.data(), (long long*)work.prof.p + (size_t)ctas * 8, 64 * sizeof(long long), cudaMemcpyDeviceToHost));
+      if (tr[0] != 0) {
+        fprintf(stderr, "[fused trace] CTA 0, third item (cycles from its stage-0 start): MMA warp: start / first granule / last granule / all issued | "
+                        "epilogue warp 4: accumulator seen / first granule written / last written\n");
+        for (int q = 0; q < g.nstages; q++)
+          fprintf(stderr, "  S%d (K %3d N %3d): %6lld %6lld %6lld %6lld | %6lld %6lld %6lld\n", q, g.K[q], g.N[q], tr[q * 8] - tr[0], tr[q * 8 + 1] ? tr[q * 8 + 1] - tr[0] : 0,
+                  tr[q * 8 + 2] ? tr[q * 8 + 2] - tr[0] : 0, tr[q * 8 + 3] - tr[0], tr[q * 8 + 4] - tr[0], tr[q * 8 + 5] ? tr[q * 8 + 5] - tr[0] : 0, tr[q * 8 + 6] - tr[0]);
+      }
       double s[8] = {0, 0, 0, 0, 0, 0, 0, 0};
       for (int c = 0; c < grid; c++)
         for (int k = 0; k < 8; k++) s[k] += (double)h[(size_t)c * 8 + k] / grid;
