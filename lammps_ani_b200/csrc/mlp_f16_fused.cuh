@@ -414,13 +414,15 @@ f16_fused_kernel(const __grid_constant__ FusedMaps maps, const __grid_constant__
     // written back over itself (tcgen05.st: 8 columns hi, 8 columns lo); the MMA warp is told per granule.  The four warps of a
     // quadrant work on four different granules at once, so granules complete in bursts of four, 64 columns = two weight
     // k-blocks, and the next stage's MMAs trail by at most that.
-    const int q = warp & 3, j8 = (warp - 4) >> 2;                 // lane quadrant, granule phase (and 8-column slice in S5)
+    // The warp scheduler favours the highest warp ids of a sub-partition: they take the EARLIEST granules, so that the first
+    // granule pair of a stage -- what the next stage's MMAs wait for -- is finished first instead of last.
+    const int q = warp & 3, j8 = 3 - ((warp - 4) >> 2);           // lane quadrant, granule phase (and 8-column slice in S5)
     const int r = q * 32 + lane;                                  // row inside the 128-row tile
     float4* const scr = (float4*)(g.scratch + (size_t)blockIdx.x * g.scratch_per_cta);
     const int n1 = g.N[0];
     uint32_t hpar = 0, t = 0, cuse[2] = {0, 0};                   // hpar bit i: parity of this warp's uses of output-block slot i
     long long w_acc = 0, w_h = 0, t_begin = 0;
-    const bool prof_me = PROF && warp == 4 && lane == 0;
+    const bool prof_me = PROF && warp == 16 && lane == 0;     // (the warp that takes granule 0)
     if (prof_me) t_begin = clock64();
     // float4 index of (granule gi, quadrant q, vector 0, lane) in a CELU' scratch area (vector v is 32 float4 further on): a
     // warp's store / load of one vector is 512 contiguous bytes, and a value is read back by the thread that wrote it
@@ -530,7 +532,7 @@ f16_fused_kernel(const __grid_constant__ FusedMaps maps, const __grid_constant__
               d[e] = fminf(exp2f(u), 1.f);                                      // CELU'(z) = min(e^(z/alpha), 1)
               h[c4 * 4 + e] = fmaxf(u, fmaf(kFCeluC, d[e], -kFCeluC));          // kFScaleH * CELU(z)   (e^x - 1 >= x)
             }
-            __stcg(dp + c4 * 32, make_float4(d[0], d[1], d[2], d[3]));
+            dp[c4 * 32] = make_float4(d[0], d[1], d[2], d[3]);      // plain (weak) store: read back by this same thread only
           }
           emit_tmem(gi, h);
         }
@@ -773,7 +775,7 @@ inline int mlp_species_fused(cudaStream_t st, SpeciesWeights& w, FusedWork& work
       ANIB_CUDA_OK(cudaMemcpy(tr.data(), (long long*)work.prof.p + (size_t)ctas * 8, 64 * sizeof(long long), cudaMemcpyDeviceToHost));
       if (tr[0] != 0) {
         fprintf(stderr, "[fused trace] CTA 0, third item (cycles from its stage-0 start): MMA warp: start / first granule / last granule / all issued | "
-                        "epilogue warp 4: accumulator seen / first granule written / last written\n");
+                        "epilogue warp 16 (granules 0, 4, ..): accumulator seen / first granule written / last written\n");
         for (int q = 0; q < g.nstages; q++)
           fprintf(stderr, "  S%d (K %3d N %3d): %6lld %6lld %6lld %6lld | %6lld %6lld %6lld\n", q, g.K[q], g.N[q], tr[q * 8] - tr[0], tr[q * 8 + 1] ? tr[q * 8 + 1] - tr[0] : 0,
                   tr[q * 8 + 2] ? tr[q * 8 + 2] - tr[0] : 0, tr[q * 8 + 3] - tr[0], tr[q * 8 + 4] - tr[0], tr[q * 8 + 5] ? tr[q * 8 + 5] - tr[0] : 0, tr[q * 8 + 6] - tr[0]);
@@ -783,7 +785,7 @@ inline int mlp_species_fused(cudaStream_t st, SpeciesWeights& w, FusedWork& work
         for (int k = 0; k < 8; k++) s[k] += (double)h[(size_t)c * 8 + k] / grid;
       const double per = (double)items / grid;
       fprintf(stderr, "[fused prof] K0 %d widths %d-%d-%d rows %d items %d grid %d | per item (cycles): MMA thread total %.0f, waits: acc-free %.0f weights %.0f A-block %.0f, issue+commit %.0f"
-              " | epilogue warp 4 total %.0f, waits: acc-full %.0f slot %.0f\n",
+              " | epilogue warp 16 total %.0f, waits: acc-full %.0f slot %.0f\n",
               Lin, n1, n2, n3, Rc, items, grid, s[0] / per, s[1] / per, s[2] / per, s[3] / per, s[7] / per, s[4] / per, s[5] / per, s[6] / per);
     }
     if (!fuse_d) {
