@@ -62,7 +62,9 @@ int ani_ctx_set_mlp_mode(ani_ctx* ctx, int mode); /* enum ani_mlp_mode; single p
 int ani_ctx_set_stream(ani_ctx* ctx, void* cuda_stream);
 int ani_ctx_reset_stream(ani_ctx* ctx);
 /* Waits for the context's stream AND reports (once) any device-side error flag a step that was not synchronised raised:
- * 2 = more angular neighbours than the kernels hold, 3 = an MLP value left the fp16 operand range of the f16x3 path.  */
+ * 2 = more angular neighbours than the kernels hold, 3 = a value left the numeric range of a kernel (an MLP activation or gradient
+ * outside the fp16 operand range of the f16x3 path, or an angular force term outside the fixed-point range of the fp32 AEV backward
+ * kernel): ani_last_error() says which; the step's result is invalid.  */
 int ani_ctx_synchronize(ani_ctx* ctx);
 /* Per-context switches (the reference has only LAMMPS_ANI_ALLOW_TF32 / LAMMPS_ANI_PROFILING, ani.cpp:41, pair_ani.cpp:49).
  * "mlp_fused" 1 (default): the f16x3 MLP of a species bucket runs as one fused kernel, 0: layer by layer;

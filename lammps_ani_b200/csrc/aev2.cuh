@@ -75,6 +75,7 @@ struct Aev2Rows {
   int* ovf_rows = nullptr;
   const int* sel_cnt = nullptr;
   const int* sel_rows = nullptr;
+  int* range_flag = nullptr;     // backward pass, fp32: bit 1 is set when an angular gradient term leaves the fixed-point range
 };
 
 // ------------------------------------------------------------------------------------------------ forward
@@ -460,8 +461,11 @@ aev2_backward_row(const AevConst<T>& P, int radial_filter, const typename Vec4T<
 
   // fp32: the per-neighbour angular gradients are summed in 2^-36 fixed point, split into two int32 words (q = hi * 2^24 + lo,
   // lo in [0, 2^24)): shared-memory integer adds are native, float adds are compare-and-swap loops; a neighbour receives at most
-  // na - 1 <= 95 contributions, so neither word overflows for |term| < 5000, and the sum does not depend on the order
+  // na - 1 <= 95 contributions, so neither word overflows for |term| < 5000, and the sum does not depend on the order.
+  // The bound is checked: a lane that saw a triple whose six terms sum (in absolute value) to 4096 or more, or to NaN, raises
+  // bit 1 of rs.range_flag, which the host reports as status 3 (two atoms nearly on top of each other: the step is invalid).
   constexpr bool kFixed = sizeof(T) == 4;
+  bool bad = false;
   if (kFixed)
     for (int e = lane; e < na * 6; e += 32) sh_gi[e] = 0;
   // ---- radial: lane = neighbour
@@ -531,6 +535,8 @@ aev2_backward_row(const AevConst<T>& P, int radial_filter, const typename Vec4T<
       const T gbx = dE_drb * B.x + kb * (A.x - cosv * B.x), gby = dE_drb * B.y + kb * (A.y - cosv * B.y),
               gbz = dE_drb * B.z + kb * (A.z - cosv * B.z);
       if (kFixed) {
+        const float l1 = fabsf((float)gax) + fabsf((float)gay) + fabsf((float)gaz) + fabsf((float)gbx) + fabsf((float)gby) + fabsf((float)gbz);
+        bad |= !(l1 < 4096.0f);                                                  // true for NaN as well
         auto fx_add = [&](int word, T v) {
           const long long q = __float2ll_rn((float)v * 68719476736.0f);          // 2^36
           atomicAdd(sh_gi + word, (int)(q >> 24));
@@ -547,6 +553,7 @@ aev2_backward_row(const AevConst<T>& P, int radial_filter, const typename Vec4T<
   }
   __syncwarp();
   if (kFixed) {   // fold the fixed-point sums into the per-neighbour gradients (one angular slot per neighbour: no conflicts)
+    if (bad && rs.range_flag != nullptr) atomicOr(rs.range_flag, 2);
     for (int a = lane; a < na; a += 32) {
       const int ea = sh_ai[a];
 #pragma unroll

@@ -247,7 +247,7 @@ struct Engine : EngineBase {
       for (int t = s; t < hm.S; t++) { P.triu[s][t] = p; P.triu[t][s] = p; p++; }
     Pfull = P;
     nets.resize(hm.S);
-    ANIB_RESERVE(d_err, 2 * sizeof(int));   // [0] angular-neighbour overflow, [1] fp16 operand range (mlp_f16_fused.cuh)
+    ANIB_RESERVE(d_err, 2 * sizeof(int));   // [0] angular-neighbour overflow, [1] bit 0 fp16 operand range (mlp_f16_fused.cuh), bit 1 fixed-point range (aev2.cuh backward)
     ANIB_CUDA_OK(cudaMemset(d_err.p, 0, 2 * sizeof(int)));
     ANIB_RESERVE(d_scalars, 16 * sizeof(double));
     ANIB_RESERVE(d_virial, kVirialSlots * 9 * sizeof(double));
@@ -709,6 +709,7 @@ struct Engine : EngineBase {
         ANIB_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem2));
         const int grid = (nlocal + kAev2Warps - 1) / kAev2Warps;
         Aev2Rows rs;
+        rs.range_flag = d_err.as<int>() + 1;
         if (two_pass) {
           const Aev2Layout L1 = aev2_layout<T>(cap1, capA1, acc_b, P.nZ, P.nA, true);
           rs.ovf_cnt = d_ovf.as<int>() + 3; rs.ovf_rows = d_ovf_rows.as<int>() + nlocal;
@@ -718,6 +719,7 @@ struct Engine : EngineBase {
               (T)kHartree2KcalMol, cap1, capA1, L1.bytes, rs);
           c->launches++;
           rs = Aev2Rows();
+          rs.range_flag = d_err.as<int>() + 1;
           rs.sel_cnt = d_ovf.as<int>() + 3; rs.sel_rows = d_ovf_rows.as<int>() + nlocal;
         }
         if (two_pass) {
@@ -847,6 +849,11 @@ struct Engine : EngineBase {
     herr[0] = herr[1] = 0;
     cudaMemsetAsync(d_err.p, 0, 2 * sizeof(int), c->stream);
     if (e0) { set_error("an atom has more than " + std::to_string(capA) + " neighbours inside the angular cutoff"); return 2; }
+    if (e1 & 2) {
+      set_error("an angular force term left the fixed-point range of the fp32 AEV backward kernel (|term| >= 4096 Hartree/A or NaN: "
+                "two atoms are nearly on top of each other); the result of this step is invalid");
+      return 3;
+    }
     set_error("an MLP activation or gradient left the fp16 operand range of the f16x3 tensor-core path (|16 h| or |256 g| >= 65504): "
               "the result of this step is invalid; use ani_ctx_set_mlp_mode(ANI_MLP_TF32X3 or ANI_MLP_FP32_SIMT) for this system");
     return 3;

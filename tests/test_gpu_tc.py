@@ -188,3 +188,22 @@ def test_f16_operand_range_guard(runner, tmp_path, fused):
     ani2.set_mlp_mode(runner.MLP_FP32_SIMT)
     e, f, _, _ = ani2.compute(sub.species, sub.x, il, jl, nn, nlocal=sub.nlocal, ago=0)
     assert np.isfinite(e) and np.isfinite(f).all()
+
+
+def test_fixed_point_range_guard(runner, ani2x_synth_path):
+    """the fp32 AEV backward kernel sums angular gradient terms in 2^-36 fixed point, which holds |term| < ~5000.
+    Two atoms 1e-6 A apart give terms of order dE/dcos / r far beyond that: the library must report status 3 instead of
+    returning wrapped-around forces; the next (sane) step on the same context is clean."""
+    x, sp, box = domain.make_water_box((5, 5, 5), seed=3)
+    sub = domain.decompose(x, sp, box)[0]
+    good = sub.x.copy()
+    bad = good - (good[0] - 0.25)                 # atom 0 at (0.25, 0.25, 0.25): 2^-20 A is exact in fp32 there
+    bad[1] = bad[0] + np.array([2.0 ** -20, 0.0, 0.0])
+    ani = runner.ANI(ani2x_synth_path, 0, -1, True, True, True)
+    ani.set_mlp_mode(runner.MLP_FP32_SIMT)        # no fp16 planes involved: only the fixed-point guard can fire
+    il, nn, jl = domain.full_neighbor_list(bad, sub.nlocal)
+    with pytest.raises(RuntimeError, match="fixed-point range"):
+        ani.compute(sub.species, bad, il, jl, nn, nlocal=sub.nlocal, ago=0)
+    il, nn, jl = domain.full_neighbor_list(good, sub.nlocal)
+    e, f, _, _ = ani.compute(sub.species, good, il, jl, nn, nlocal=sub.nlocal, ago=0)
+    assert np.isfinite(e) and np.isfinite(f).all()
