@@ -849,13 +849,13 @@ struct Engine : EngineBase {
     herr[0] = herr[1] = 0;
     cudaMemsetAsync(d_err.p, 0, 2 * sizeof(int), c->stream);
     if (e0) { set_error("an atom has more than " + std::to_string(capA) + " neighbours inside the angular cutoff"); return 2; }
-    if (e1 & 2) {
-      set_error("an angular force term left the fixed-point range of the fp32 AEV backward kernel (|term| >= 4096 Hartree/A or NaN: "
-                "two atoms are nearly on top of each other); the result of this step is invalid");
+    if (e1 & 1) {      // reported first: gradients that left the fp16 planes as inf also trip the fixed-point check downstream
+      set_error("an MLP activation or gradient left the fp16 operand range of the f16x3 tensor-core path (|16 h| or |256 g| >= 65504): "
+                "the result of this step is invalid; use ani_ctx_set_mlp_mode(ANI_MLP_TF32X3 or ANI_MLP_FP32_SIMT) for this system");
       return 3;
     }
-    set_error("an MLP activation or gradient left the fp16 operand range of the f16x3 tensor-core path (|16 h| or |256 g| >= 65504): "
-              "the result of this step is invalid; use ani_ctx_set_mlp_mode(ANI_MLP_TF32X3 or ANI_MLP_FP32_SIMT) for this system");
+    set_error("an angular force term left the fixed-point range of the fp32 AEV backward kernel (|term| >= 4096 Hartree/A or NaN: "
+              "two atoms are nearly on top of each other); the result of this step is invalid");
     return 3;
   }
 
