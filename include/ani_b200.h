@@ -154,6 +154,15 @@ int ani_md_nve_final(ani_ctx* ctx, double* v_dev, const double* f_dev, const dou
 int ani_md_langevin(ani_ctx* ctx, const double* v_dev, double* f_dev, const double* mass_dev, const int64_t* tag_dev, int n,
                     double g1, double g2, uint64_t seed, int64_t step);
 int ani_md_sum_mv2(ani_ctx* ctx, const double* v_dev, const double* mass_dev, int n, double* out_host);
+/* Allocation-free variant of ani_md_sum_mv2.  It has no counterpart in the reference and was added
+ * for callers that cannot allocate (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc): it calls no cudaMalloc / cudaFree / allocating routine and does not synchronise.  The per-block partial sums go
+ * to a file-scope static device array (1024 doubles = 8 KB, held by every GPU that loads the library until the process exits);
+ * the sum is written to out_dev[0] (DEVICE pointer, one double) in the order of the context's stream.  n must be within
+ * 0 .. 16 777 216 atoms (ANI_MD_SUM_MV2_STATIC_MAX); beyond that the call fails with status 1 and a message.  All calls on a
+ * device share the one scratch array: two calls that overlap on the GPU (different streams / contexts) race -- serialise them. */
+#define ANI_MD_SUM_MV2_STATIC_MAX 16777216
+int ani_md_sum_mv2_static(ani_ctx* ctx, const double* v_dev, const double* mass_dev, int n, double* out_dev);
 int ani_md_ghost_x(ani_ctx* ctx, double* x_dev, const int* owner_dev, const double* shift_dev, int nlocal, int nghost);
 int ani_md_fold_ghost_f(ani_ctx* ctx, double* f_dev, const int* owner_dev, int nlocal, int nghost);
 

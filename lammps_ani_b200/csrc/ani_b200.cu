@@ -1405,6 +1405,41 @@ int ani_md_sum_mv2(ani_ctx* c, const double* v_dev, const double* mass_dev, int 
   return 0;
 }
 
+// Allocation-free variant of ani_md_sum_mv2 (no counterpart in the reference; added for
+// callers that cannot allocate: CUDA graph capture, tight serving loops).  No cudaMalloc / cudaFree / host container: the
+// partials go to the file-scope array g_mv2_static_scratch (md.cuh), whose DEVICE address is looked up once per device with
+// cudaGetSymbolAddress (in host code the array's name is only a host-side stand-in), and the sum lands in out_dev[0] in stream
+// order; nothing synchronises.  All calls on a device share the one array: calls that overlap on the GPU (different streams or
+// contexts) race.  Nothing needs zeroing: a call overwrites every partial it later reads.
+int ani_md_sum_mv2_static(ani_ctx* c, const double* v_dev, const double* mass_dev, int n, double* out_dev) {
+  if (!c || !out_dev || (n > 0 && (!v_dev || !mass_dev))) { set_error("ani_md_sum_mv2_static: null argument"); return 1; }
+  if (n < 0 || n > kMv2StaticMaxAtoms) {
+    set_error("ani_md_sum_mv2_static: n = " + std::to_string(n) + " is outside 0 .. " + std::to_string(kMv2StaticMaxAtoms) +
+              " (the limit of the static scratch variant; use ani_md_sum_mv2)");
+    return 1;
+  }
+  ANIB_CUDA_OK(cudaSetDevice(c->device));
+  constexpr int kMaxDev = 64;
+  static double* scratch_of[kMaxDev] = {};              // device address of the array on each GPU, filled on first use
+  static std::mutex mu;
+  if (c->device < 0 || c->device >= kMaxDev) { set_error("ani_md_sum_mv2_static: device index out of range"); return 1; }
+  double* part = nullptr;
+  {
+    std::lock_guard<std::mutex> lk(mu);
+    if (!scratch_of[c->device]) {
+      void* p = nullptr;
+      ANIB_CUDA_OK(cudaGetSymbolAddress(&p, g_mv2_static_scratch));     // with c->device current: the address is per device
+      scratch_of[c->device] = (double*)p;
+    }
+    part = scratch_of[c->device];
+  }
+  const int nb = std::max(1, std::min(kMv2StaticBlocks, (n + 255) / 256));
+  md_mv2_kernel<<<nb, 256, 0, c->stream>>>(v_dev, mass_dev, n, part);     // n == 0: one block writes partial[0] = 0
+  md_mv2_final_kernel<<<1, 256, 0, c->stream>>>(part, nb, out_dev);
+  ANIB_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
 int ani_md_ghost_x(ani_ctx* c, double* x_dev, const int* owner_dev, const double* shift_dev, int nlocal, int nghost) {
   if (!c || (nghost > 0 && (!x_dev || !owner_dev || !shift_dev))) { set_error("ani_md_ghost_x: null argument"); return 1; }
   if (nghost <= 0) return 0;

@@ -78,6 +78,26 @@ __global__ void md_mv2_kernel(const double* __restrict__ v, const double* __rest
   if (threadIdx.x == 0) partial[blockIdx.x] = sh[0];
 }
 
+// ---- allocation-free variant of the sum (ani_md_sum_mv2_static): the per-block partials live in a file-scope device array
+// instead of a stream-ordered allocation.  Every GPU that loads the library holds these 8 KB until the process exits.
+constexpr int kMv2StaticBlocks = 1024;                 // partials held by the static scratch
+constexpr int kMv2StaticMaxAtoms = 1 << 24;            // stated limit of the entry point (16 777 216 atoms: 64 grid-stride passes)
+static __device__ __align__(256) double g_mv2_static_scratch[kMv2StaticBlocks];
+
+// second stage: one block adds the nb <= 1024 partials in a fixed order (the result does not depend on the launch) -> out[0]
+__global__ void md_mv2_final_kernel(const double* __restrict__ partial, int nb, double* __restrict__ out) {
+  __shared__ double sh[256];
+  double s = 0.0;
+  for (int i = threadIdx.x; i < nb; i += 256) s += partial[i];
+  sh[threadIdx.x] = s;
+  __syncthreads();
+  for (int w = 128; w > 0; w >>= 1) {
+    if ((int)threadIdx.x < w) sh[threadIdx.x] += sh[threadIdx.x + w];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) out[0] = sh[0];
+}
+
 // ghost-force fold for a single periodic domain: f[owner[g]] += f[nlocal + g]   (pair_ani.cpp:461-484 with every ghost a self image)
 __global__ void md_fold_ghost_kernel(double* __restrict__ f, const int* __restrict__ owner, int nlocal, int nghost) {
   const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
