@@ -34,10 +34,12 @@ namespace anib {
 namespace f16 {
 
 constexpr int kFusedMaxStages = 6;
-constexpr int kFG = 4;                          // epilogue groups = output-block slots
+constexpr int kFG = 4;                          // epilogue groups (four warps each)
+constexpr int kFH = 2;                          // output-block slots of the last stage (a power of two <= kFG)
 constexpr int kFThreads = 128 + 128 * kFG;
 constexpr int kFNB = 4;                         // weight ring depth
-constexpr int kFNA = 2;                         // AEV ring depth
+constexpr int kFNA = 4;                         // AEV ring depth: the next item's whole tile (K <= 128) is prefetched during the current
+                                                // item's last stage; with two blocks stage 0 waited ~1.3 k cycles for each of the others
 constexpr int kFBSlot = 32768;                  // one weight k-block: 256 rows x 32 halves x (hi + lo)
 constexpr int kFBlk = 16384;                    // 128 rows x 32 halves x (hi + lo), or 128 rows x 32 floats
 constexpr int kFGran = 16;                       // 16-column granules of a stage (N <= 256)
@@ -172,7 +174,7 @@ __device__ __forceinline__ void tma_reduce_add_2d(const CUtensorMap* tm, uint32_
   asm volatile("cp.reduce.async.bulk.tensor.2d.global.shared::cta.add.tile.bulk_group [%0, {%2, %3}], [%1];" ::"l"(tm), "r"(src),
                "r"(c0), "r"(c1) : "memory");
 }
-__device__ __forceinline__ int fused_uses(int nb, int g) { return (nb - g + kFG - 1) / kFG; }   // blocks cb < nb with cb % kFG == g
+__device__ __forceinline__ int fused_uses(int nb, int g) { return (nb - g + kFH - 1) / kFH; }   // blocks cb < nb with cb % kFH == g
 
 // ---- epilogue pieces: 8 columns at a time (one 16-byte chunk of the hi plane and one of the lo plane)
 __device__ __forceinline__ void put_planes8(uint32_t blk, int r, int ch, const float (&x)[8], float& amax) {
@@ -196,7 +198,7 @@ f16_fused_kernel(const __grid_constant__ FusedMaps maps, const __grid_constant__
   const uint32_t baseB = raw;
   const uint32_t baseA = baseB + (uint32_t)kFNB * kFBSlot;
   const uint32_t baseH = baseA + (uint32_t)kFNA * kFBlk;
-  const uint32_t baseC = baseH + (uint32_t)kFG * kFBlk;           // two slots of per-stage constants
+  const uint32_t baseC = baseH + (uint32_t)kFH * kFBlk;           // two slots of per-stage constants
   const uint32_t bar_base = baseC + 2u * (uint32_t)g.cslot_bytes;
   auto bfull = [&](int i) { return bar_base + 8u * (uint32_t)i; };
   auto bempty = [&](int i) { return bar_base + 8u * (uint32_t)(kFNB + i); };
@@ -389,7 +391,7 @@ f16_fused_kernel(const __grid_constant__ FusedMaps maps, const __grid_constant__
       for (int it = blockIdx.x; it < num_items; it += gridDim.x) {
         const int rt = it / g.batch, z = it % g.batch;
         for (int cb = 0; cb < nb; cb++) {
-          const int slot = cb % kFG;
+          const int slot = cb % kFH;
           mbar_wait_wd(dfull(slot), dcnt[slot] & 1u, g.dbg, WD(10, slot));
           dcnt[slot]++;
           const uint32_t src = baseH + (uint32_t)slot * kFBlk;
@@ -486,7 +488,7 @@ f16_fused_kernel(const __grid_constant__ FusedMaps maps, const __grid_constant__
       // the same 16 values into an output block in shared memory (the K-major SWIZZLE_64B layout of the g1 planes' TMA store);
       // granules 2 cb and 2 cb + 1 make block cb
       auto emit_smem = [&](int gi, const float (&x)[16]) {
-        const int slot = (gi >> 1) & (kFG - 1);
+        const int slot = (gi >> 1) & (kFH - 1);
         wait_slot(slot);
         const uint32_t dstb = baseH + (uint32_t)slot * kFBlk;
 #pragma unroll
@@ -618,7 +620,7 @@ f16_fused_kernel(const __grid_constant__ FusedMaps maps, const __grid_constant__
         wait_acc();
 #pragma unroll 1
         for (int cb = 0; cb < nb; cb++) {
-          const int slot = cb & (kFG - 1);
+          const int slot = cb & (kFH - 1);
           uint32_t v[8];
           tmem_ld8(tslice(cb), v);
           wait_slot(slot);
@@ -697,7 +699,7 @@ inline int mlp_species_fused(cudaStream_t st, SpeciesWeights& w, FusedWork& work
   }
   const int Lin = dims[0], n1 = dims[1], n2 = dims[2], n3 = dims[3];
   const int cslot = (std::max(std::max(n1, n2), 2 * n3) * 4 + 127) / 128 * 128;
-  const int smem = kFNB * kFBSlot + (kFNA + kFG) * kFBlk + 2 * cslot + 8 * kFBars + 16;
+  const int smem = kFNB * kFBSlot + (kFNA + kFH) * kFBlk + 2 * cslot + 8 * kFBars + 16;
   if (smem > max_smem) { set_error("not enough shared memory for the fused f16 MLP kernel"); return 1; }
   const int Npad = (Lin + 31) / 32 * 32;
   const bool fuse_d = Npad <= 256;
