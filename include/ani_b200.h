@@ -74,6 +74,11 @@ int ani_ctx_synchronize(ani_ctx* ctx);
  * fused kernel's cycle counters to stderr.  The environment (ANI_B200_FUSED, ANI_B200_AEV_TWO_PASS, ANI_B200_GEMM_CTAS,
  * ANI_B200_FUSED_PROF) only sets the defaults a context starts with. */
 int ani_ctx_set_option(ani_ctx* ctx, const char* name, int value);
+/* Page-lock a caller array (cudaHostRegister) so that ani_dev_upload / ani_dev_download / ani_compute on it are direct DMA
+ * instead of staged copies (LAMMPS's atom->x, v, f are pageable: 6 GB/s staged, > 25 GB/s pinned).  The registration is dropped
+ * by ani_ctx_release_host_buffers, which the caller MUST call before the array is freed or reallocated (the pair style does when
+ * atom->nmax changes), and by ani_ctx_destroy.  An array that is already registered is accepted as is. */
+int ani_ctx_pin_host(ani_ctx* ctx, void* host, size_t bytes);
 
 /* ---- neighbour data: call when the list was rebuilt (neighbor->ago == 0, pair_ani.cpp:107-151) ---------
  * species[ntotal] = LAMMPS type-1 for local AND ghost atoms (pair_ani.cpp:109-111).
@@ -154,6 +159,11 @@ int ani_md_nve_final(ani_ctx* ctx, double* v_dev, const double* f_dev, const dou
 int ani_md_langevin(ani_ctx* ctx, const double* v_dev, double* f_dev, const double* mass_dev, const int64_t* tag_dev, int n,
                     double g1, double g2, uint64_t seed, int64_t step);
 int ani_md_sum_mv2(ani_ctx* ctx, const double* v_dev, const double* mass_dev, int n, double* out_host);
+/* max_i |x_i - x0_i|^2 over n atoms, to the host (synchronises): the displacement test of Neighbor::check_distance
+ * (external/lammps/src/neighbor.cpp: rebuild when an atom has moved more than half the skin since the last build) without
+ * copying the positions to the host.  fix ani/md asks it on the steps where neighbor->decide() would look at atom->x and
+ * only brings x, v back when the answer says LAMMPS will rebuild. */
+int ani_md_max_disp2(ani_ctx* ctx, const double* x_dev, const double* x0_dev, int n, double* out_host);
 /* Allocation-free variant of ani_md_sum_mv2.  It has no counterpart in the reference and was added
  * for callers that cannot allocate (code under CUDA graph capture, tight serving loops, harnesses that forbid
  * cudaMalloc): it calls no cudaMalloc / cudaFree / allocating routine and does not synchronise.  The per-block partial sums go

@@ -171,6 +171,10 @@ struct ani_ctx {
   std::vector<int64_t> h_beg;
   std::vector<int> h_cnt, h_species, h_tmp;
   std::vector<int> h_jl;
+  // caller arrays page-locked on request (ani_ctx_pin_host), released by ani_ctx_release_host_buffers / destroy
+  std::vector<void*> pinned_host;
+  unsigned long long* d_word = nullptr;      // one device word + its pinned host mirror (ani_md_max_disp2)
+  unsigned long long* h_word = nullptr;
 };
 
 namespace anib {
@@ -1037,6 +1041,9 @@ void ani_ctx_destroy(ani_ctx* c) {
   if (!c) return;
   cudaSetDevice(c->device);
   c->eng.reset();
+  for (void* q : c->pinned_host) { cudaHostUnregister(q); cudaGetLastError(); }
+  if (c->d_word) cudaFree(c->d_word);
+  if (c->h_word) cudaFreeHost(c->h_word);
   for (int q = 0; q < 6; q++) if (c->ev[q]) cudaEventDestroy(c->ev[q]);
   if (c->own_stream) cudaStreamDestroy(c->own_stream);
   delete c;
@@ -1116,7 +1123,21 @@ int ani_ctx_release_host_buffers(ani_ctx* c) {
   if (!c) { set_error("null context"); return 1; }
   ANIB_CUDA_OK(cudaSetDevice(c->device));
   c->eng->release_pins();
+  for (void* q : c->pinned_host) { cudaHostUnregister(q); cudaGetLastError(); }
+  c->pinned_host.clear();
   return 0;
+}
+
+int ani_ctx_pin_host(ani_ctx* c, void* host, size_t bytes) {
+  if (!c) { set_error("null context"); return 1; }
+  if (!host || !bytes) return 0;
+  ANIB_CUDA_OK(cudaSetDevice(c->device));
+  const cudaError_t rc = cudaHostRegister(host, bytes, cudaHostRegisterDefault);
+  if (rc == cudaSuccess) { c->pinned_host.push_back(host); return 0; }
+  cudaGetLastError();
+  if (rc == cudaErrorHostMemoryAlreadyRegistered) return 0;       // the caller (or an earlier call) pinned it: nothing to do
+  set_error(std::string("ani_ctx_pin_host: cudaHostRegister failed: ") + cudaGetErrorString(rc));
+  return 1;
 }
 
 int ani_debug_get_neighbors(ani_ctx* c, int* numneigh, int* jlist) {
@@ -1403,6 +1424,23 @@ int ani_md_sum_mv2(ani_ctx* c, const double* v_dev, const double* mass_dev, int 
   ANIB_CUDA_OK(cudaStreamSynchronize(c->stream));
   for (double q : h) *out_host += q;
   return 0;
+}
+
+int ani_md_max_disp2(ani_ctx* c, const double* x_dev, const double* x0_dev, int n, double* out_host) {
+  if (!c || !out_host || (n > 0 && (!x_dev || !x0_dev))) { set_error("ani_md_max_disp2: null argument"); return 1; }
+  *out_host = 0.0;
+  if (n <= 0) return 0;
+  ANIB_CUDA_OK(cudaSetDevice(c->device));
+  if (!c->d_word) {
+    ANIB_CUDA_OK(cudaMalloc((void**)&c->d_word, sizeof(unsigned long long)));
+    ANIB_CUDA_OK(cudaMallocHost((void**)&c->h_word, sizeof(unsigned long long)));
+  }
+  ANIB_CUDA_OK(cudaMemsetAsync(c->d_word, 0, sizeof(unsigned long long), c->stream));
+  md_max_disp2_kernel<<<std::min(592, (n + 255) / 256), 256, 0, c->stream>>>(x_dev, x0_dev, n, c->d_word);
+  ANIB_CUDA_OK(cudaMemcpyAsync(c->h_word, c->d_word, sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
+  ANIB_CUDA_OK(cudaStreamSynchronize(c->stream));
+  memcpy(out_host, c->h_word, sizeof(double));
+  return c->eng ? c->eng->check_errors() : 0;
 }
 
 // Allocation-free variant of ani_md_sum_mv2 (no counterpart in the reference; added for

@@ -78,6 +78,25 @@ __global__ void md_mv2_kernel(const double* __restrict__ v, const double* __rest
   if (threadIdx.x == 0) partial[blockIdx.x] = sh[0];
 }
 
+// max_i |x_i - x0_i|^2 over the local atoms (Neighbor::check_distance, external/lammps/src/neighbor.cpp, on the device): the bits
+// of a non-negative double order like the number, so one atomicMax on the 64-bit pattern per block does it
+__global__ void md_max_disp2_kernel(const double* __restrict__ x, const double* __restrict__ x0, int n, unsigned long long* __restrict__ out) {
+  __shared__ double sh[256];
+  double m = 0.0;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const double a = x[3 * (size_t)i] - x0[3 * (size_t)i], b = x[3 * (size_t)i + 1] - x0[3 * (size_t)i + 1],
+                 c = x[3 * (size_t)i + 2] - x0[3 * (size_t)i + 2];
+    m = fmax(m, a * a + b * b + c * c);
+  }
+  sh[threadIdx.x] = m;
+  __syncthreads();
+  for (int w = 128; w > 0; w >>= 1) {
+    if ((int)threadIdx.x < w) sh[threadIdx.x] = fmax(sh[threadIdx.x], sh[threadIdx.x + w]);
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) atomicMax(out, (unsigned long long)__double_as_longlong(sh[0]));
+}
+
 // ---- allocation-free variant of the sum (ani_md_sum_mv2_static): the per-block partials live in a file-scope device array
 // instead of a stream-ordered allocation.  Every GPU that loads the library holds these 8 KB until the process exits.
 constexpr int kMv2StaticBlocks = 1024;                 // partials held by the static scratch

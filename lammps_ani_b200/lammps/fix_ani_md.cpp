@@ -1,6 +1,7 @@
 /* fix_ani_md.cpp -- see fix_ani_md.h.  Per timestep (Verlet::run, external/lammps/src/verlet.cpp:229-360):
  *   initial_integrate : v += dtf f/m, x += dtv v on the device (ani_md_nve_initial).  If the coming neighbor->decide() will look
- *                       at positions (ago+1 reaches `every`), x and v are copied to the host first: LAMMPS may then re-wrap,
+ *                       at positions (ago+1 reaches `every`) and, with `check yes`, the device-side displacement test says an
+ *                       atom moved more than half the skin, x and v are copied to the host first: LAMMPS may then re-wrap,
  *                       sort and re-ghost them, and the pair style / this fix upload them again after the rebuild.
  *   [pair compute]    : PairANIB200::resident_compute -- ghosts from owners, forces into the device array.
  *   post_force        : Langevin forces on the device (ani_md_langevin), after re-uploading v / mass / tag if the atoms were
@@ -16,6 +17,7 @@
 #include "ani_b200.h"
 #include "atom.h"
 #include "comm.h"
+#include "domain.h"
 #include "error.h"
 #include "force.h"
 #include "neighbor.h"
@@ -112,7 +114,12 @@ void FixANIMD::initial_integrate(int) {
   // Neighbor::decide(): ago++, then a rebuild (check no) or a displacement check on atom->x (check yes) when ago >= delay and
   // ago % every == 0 -- either way LAMMPS reads, and possibly permutes, the host arrays on this step
   const int ago1 = neighbor->ago + 1;
-  if (ago1 >= neighbor->delay && ago1 % neighbor->every == 0) sync_host(false);
+  if (ago1 >= neighbor->delay && ago1 % neighbor->every == 0) {
+    // check yes, fixed box: the displacement test runs on the device first, and the host copy is only refreshed when it says
+    // LAMMPS is going to rebuild (its own test on the stale host positions then says "no", consistently)
+    const bool device_test = neighbor->dist_check && !domain->box_change && uploaded_step == pair->res.rebuilt_step;
+    if (!device_test || pair->moved_half_skin()) sync_host(false);
+  }
 }
 
 void FixANIMD::post_force(int) {

@@ -179,7 +179,7 @@ double PairANIB200::memory_usage() {
 /* ------------------------------------------------------------------------------------------------ device-resident mode */
 void PairANIB200::resident_free() {
   if (!ctx) return;
-  ani_dev_free(ctx, res.x); ani_dev_free(ctx, res.f); ani_dev_free(ctx, res.shift); ani_dev_free(ctx, res.owner);
+  ani_dev_free(ctx, res.x); ani_dev_free(ctx, res.f); ani_dev_free(ctx, res.shift); ani_dev_free(ctx, res.owner); ani_dev_free(ctx, res.x0);
   res = Resident();
 }
 
@@ -196,6 +196,16 @@ void PairANIB200::download_x() {
     fail("download of the positions failed");
 }
 
+/* Neighbor::check_distance (external/lammps/src/neighbor.cpp) on the device copy: has any local atom moved more than half the
+ * skin since the last build?  LAMMPS's own test reads atom->x, which is stale in the device-resident mode -- the fix calls
+ * this first and copies x, v back only when the answer is yes, so that a check that would not rebuild costs 8 bytes. */
+bool PairANIB200::moved_half_skin() {
+  if (!res.valid || !res.x0) return true;
+  double d2 = 0.0;
+  if (ani_md_max_disp2(ctx, res.x, res.x0, atom->nlocal, &d2)) fail("displacement check failed");
+  return d2 > 0.25 * neighbor->skin * neighbor->skin;
+}
+
 void PairANIB200::download_f() {
   if (res.valid && atom->nlocal > 0 && ani_dev_download(ctx, &atom->f[0][0], res.f, (size_t)atom->nlocal * 3 * sizeof(double)))
     fail("download of the forces failed");
@@ -210,6 +220,20 @@ void PairANIB200::resident_compute(int eflag, int vflag) {
   const int nlocal = atom->nlocal, nghost = atom->nghost, ntotal = nlocal + nghost;
   double** x = atom->x;
   if (neighbor->ago == 0 || !res.valid) {
+    // LAMMPS's per-atom arrays are pageable: page-lock them once per allocation so the rebuild-step transfers are direct DMA
+    if (atom->nmax != last_nmax) {
+      ani_ctx_release_host_buffers(ctx);
+      last_nmax = atom->nmax;
+      const size_t bytes = (size_t)atom->nmax * 3 * sizeof(double);
+      if (atom->nmax > 0 && (ani_ctx_pin_host(ctx, &atom->x[0][0], bytes) || ani_ctx_pin_host(ctx, &atom->v[0][0], bytes) ||
+                             ani_ctx_pin_host(ctx, &atom->f[0][0], bytes)))
+        fail("page-locking the atom arrays failed");
+    }
+    if (nlocal > res.cap_x0) {
+      ani_dev_free(ctx, res.x0);
+      res.cap_x0 = nlocal + nlocal / 8 + 64;
+      if (ani_dev_alloc(ctx, (size_t)res.cap_x0 * 3 * sizeof(double), (void**)&res.x0)) fail("device allocation failed");
+    }
     if (ntotal > res.cap_total || nghost > res.cap_ghost) {
       ani_dev_free(ctx, res.x); ani_dev_free(ctx, res.f); ani_dev_free(ctx, res.shift); ani_dev_free(ctx, res.owner);
       res.cap_total = ntotal + ntotal / 8 + 64; res.cap_ghost = nghost + nghost / 8 + 64;
@@ -238,6 +262,7 @@ void PairANIB200::resident_compute(int eflag, int vflag) {
       for (int d = 0; d < 3; d++) h_shift[3 * (size_t)g + d] = x[nlocal + g][d] - x[o][d];
     }
     if (ani_dev_upload(ctx, res.x, ntotal > 0 ? &x[0][0] : nullptr, (size_t)ntotal * 3 * sizeof(double)) ||
+        ani_dev_upload(ctx, res.x0, nlocal > 0 ? &x[0][0] : nullptr, (size_t)nlocal * 3 * sizeof(double)) ||
         ani_dev_upload(ctx, res.owner, h_owner.data(), (size_t)nghost * sizeof(int)) ||
         ani_dev_upload(ctx, res.shift, h_shift.data(), (size_t)nghost * 3 * sizeof(double)))
       fail("upload failed");

@@ -59,6 +59,8 @@ class PairANIB200 : public Pair {
   struct Resident {
     bool on = false, valid = false;     // requested by a fix / device arrays hold the current state
     double *x = nullptr, *f = nullptr, *shift = nullptr;
+    double* x0 = nullptr;               // local positions at the last neighbour build (device-side displacement check)
+    int cap_x0 = 0;
     int* owner = nullptr;
     int cap_total = 0, cap_ghost = 0, nlocal = 0, nghost = 0;
     bigint rebuilt_step = -1;           // timestep of the last upload after a rebuild (the fix re-uploads v when it changes)
@@ -67,6 +69,7 @@ class PairANIB200 : public Pair {
   void set_resident(bool on);
   void download_x();                    // device -> atom->x (local atoms)
   void download_f();                    // device -> atom->f (local atoms, overwrite)
+  bool moved_half_skin();               // Neighbor::check_distance on the device arrays: true = LAMMPS will want to rebuild
 
  protected:
   void resident_compute(int eflag, int vflag);

@@ -67,6 +67,8 @@ def load_library():
     L.ani_md_langevin.argtypes = [vp, vp, vp, vp, vp, i32, C.c_double, C.c_double, C.c_uint64, i64]
     L.ani_md_sum_mv2.argtypes = [vp, vp, vp, i32, dp]
     L.ani_md_sum_mv2_static.argtypes = [vp, vp, vp, i32, vp]
+    L.ani_md_max_disp2.argtypes = [vp, vp, vp, i32, dp]
+    L.ani_ctx_pin_host.argtypes = [vp, vp, C.c_size_t]
     L.ani_md_ghost_x.argtypes = [vp, vp, vp, vp, i32, i32]
     L.ani_md_fold_ghost_f.argtypes = [vp, vp, vp, i32, i32]
     L.ani_halo_unique_id.argtypes = [C.c_char_p]
@@ -81,7 +83,7 @@ def load_library():
                  "ani_ctx_reset_stream", "ani_ctx_synchronize", "ani_ctx_enable_timing", "ani_last_timing", "ani_set_neighbors_full",
                  "ani_set_neighbors_half", "ani_set_neighbors_table", "ani_device_count", "ani_compute",
                  "ani_compute_device", "ani_debug_get_aev", "ani_halo_pack_x", "ani_halo_unpack_add_f", "ani_build_neighbors",
-                 "ani_debug_get_neighbors", "ani_md_nve_initial", "ani_md_nve_final", "ani_md_langevin", "ani_md_sum_mv2", "ani_md_sum_mv2_static",
+                 "ani_debug_get_neighbors", "ani_md_nve_initial", "ani_md_nve_final", "ani_md_langevin", "ani_md_sum_mv2", "ani_md_sum_mv2_static", "ani_md_max_disp2", "ani_ctx_pin_host",
                  "ani_md_ghost_x", "ani_md_fold_ghost_f", "ani_halo_unique_id", "ani_halo_plan_create", "ani_halo_forward",
                  "ani_halo_reverse"):
         getattr(L, name).restype = i32
@@ -95,7 +97,7 @@ EXPORTED_SYMBOLS = [
     "ani_compute_device", "ani_halo_pack_x", "ani_halo_unpack_add_f", "ani_debug_get_aev", "ani_last_timing",
     "ani_ctx_enable_timing", "ani_last_error", "ani_abi_version", "ani_debug_tc_gemm", "ani_set_neighbors_table",
     "ani_device_count", "ani_build_neighbors", "ani_debug_get_neighbors", "ani_ctx_release_host_buffers", "ani_ctx_set_option",
-    "ani_md_nve_initial", "ani_md_nve_final", "ani_md_langevin", "ani_md_sum_mv2", "ani_md_sum_mv2_static", "ani_md_ghost_x", "ani_md_fold_ghost_f",
+    "ani_md_nve_initial", "ani_md_nve_final", "ani_md_langevin", "ani_md_sum_mv2", "ani_md_sum_mv2_static", "ani_md_max_disp2", "ani_ctx_pin_host", "ani_md_ghost_x", "ani_md_fold_ghost_f",
     "ani_dev_alloc", "ani_dev_free", "ani_dev_upload", "ani_dev_download", "ani_dev_zero",
     "ani_halo_unique_id", "ani_halo_plan_create", "ani_halo_plan_destroy", "ani_halo_forward", "ani_halo_reverse",
 ]

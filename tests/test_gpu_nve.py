@@ -72,3 +72,35 @@ def test_nve_with_device_neighbor_rebuilds(ani1xnr_path):
     dev = np.abs((e - e[0]) - (e_ref - e_ref[0])).max() / n
     print(f"NVE with rebuilds: max |dE-dE_fixed-list| = {dev:.3e} kcal/mol/atom")
     assert dev <= 5e-6
+
+
+def test_max_disp2_and_pinned_host_arrays(ani2x_synth_path):
+    """ani_md_max_disp2 = Neighbor::check_distance's max |x - x0|^2 on device arrays; ani_ctx_pin_host page-locks a caller array
+    (twice is accepted), ani_dev_upload / download through it give the same bytes, release drops the registration."""
+    import ctypes as C
+    ani = runner.ANI(ani2x_synth_path, 0, -1, True, True, True)
+    L = ani._L
+    rng = np.random.default_rng(5)
+    n = 100_003
+    x0 = rng.uniform(0, 50, size=(n, 3))
+    x = x0 + rng.normal(0, 0.05, size=(n, 3))
+    x[77_001] += np.array([0.9, -0.8, 0.7])
+    dev = torch.device("cuda:0")
+    tx, tx0 = torch.from_numpy(x).to(dev), torch.from_numpy(x0).to(dev)
+    out = C.c_double()
+    assert L.ani_md_max_disp2(ani._ctx, C.c_void_p(tx.data_ptr()), C.c_void_p(tx0.data_ptr()), n, C.byref(out)) == 0
+    ref = float(((x - x0) ** 2).sum(axis=1).max())
+    assert abs(out.value - ref) <= 1e-14 * ref
+    assert L.ani_md_max_disp2(ani._ctx, C.c_void_p(tx0.data_ptr()), C.c_void_p(tx0.data_ptr()), n, C.byref(out)) == 0 and out.value == 0.0
+    # page-locked caller array: upload + download round trip
+    L.ani_dev_upload.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t]
+    L.ani_dev_download.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t]
+    host = np.ascontiguousarray(x.copy())
+    back = np.zeros_like(host)
+    for arr in (host, host, back):                      # the second registration of `host` is accepted as is
+        assert L.ani_ctx_pin_host(ani._ctx, arr.ctypes.data_as(C.c_void_p), arr.nbytes) == 0, L.ani_last_error()
+    buf = torch.empty(n * 3, dtype=torch.float64, device=dev)
+    assert L.ani_dev_upload(ani._ctx, C.c_void_p(buf.data_ptr()), host.ctypes.data_as(C.c_void_p), host.nbytes) == 0
+    assert L.ani_dev_download(ani._ctx, back.ctypes.data_as(C.c_void_p), C.c_void_p(buf.data_ptr()), back.nbytes) == 0
+    assert np.array_equal(back, host)
+    ani.release_host_buffers()

@@ -54,11 +54,22 @@ def main():
     ap.add_argument("--neighbor", default="full", help="full | half | device (list built on the GPU by the library)")
     ap.add_argument("--integrator", default="lammps", help="lammps (fix langevin + fix nve on the host) | device (fix ani/md langevin)")
     ap.add_argument("--model", default="")
+    ap.add_argument("--weight-scale", type=float, default=1.0,
+                    help="scale of the synthetic model's hidden-layer weights; 0.25 gives forces so small that the rebuild frequency is set by "
+                         "thermal motion, as with a trained potential (the default random weights heat the box to 10^4 K and every check rebuilds)")
     args = ap.parse_args()
+    if not args.model and args.weight_scale != 1.0:
+        from lammps_ani_b200 import aniw, extract
+        args.model = os.path.join(ROOT, "lammps_ani_b200", "data", f"ani2x_synthetic_seed2024_w{args.weight_scale:g}.aniw")
+        if not os.path.exists(args.model):
+            os.makedirs(os.path.dirname(args.model), exist_ok=True)
+            aniw.save(extract.synthetic_ani2x(seed=2024, weight_scale=args.weight_scale), args.model)
     if not args.model:
         import bench
         args.model = bench.model_path()
     label = "ANI-2x shapes, seeded random weights" if "synthetic" in os.path.basename(args.model) else os.path.basename(args.model)
+    if args.weight_scale != 1.0:
+        label += f" x{args.weight_scale:g} (tame forces)"
     if args.integrator == "device":
         fixes = "fix            1 all ani/md langevin 300.0 300.0 100.0 12345"
         if args.neighbor != "device":
