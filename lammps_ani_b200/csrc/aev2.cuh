@@ -29,6 +29,13 @@ struct Aev2Layout {
 
 // Forward: unsorted gather buffers (ud, us) -> species-sorted radial (r, rfc) and angular (a, afc) lists; the triple
 // batch buffers f1 / f2 alias the unsorted buffer, which is dead once the lists are sorted.
+// shared-memory words of the backward kernel's copy of the upstream gradient row: S radial rows of nR + 1 words (rounded up to
+// a multiple of four), then one row of ang_sub + 4 words per species pair
+__host__ __device__ constexpr int aev2_bwd_astride(int ang_sub) { return ang_sub + 4; }
+__host__ __device__ inline int aev2_bwd_acc_elems(int S, int nR, int npairs, int ang_sub) {
+  return (S * (nR + 1) + 3) / 4 * 4 + npairs * aev2_bwd_astride(ang_sub);
+}
+
 template <typename T>
 __host__ __device__ inline Aev2Layout aev2_layout(int cap, int capA, int acc_elems, int nZ, int nA, bool backward) {
   Aev2Layout L{};
@@ -204,6 +211,7 @@ aev2_forward_row(const AevConst<T>& P, int radial_filter, const typename Vec4T<T
 
   // ---- radial: lane = (sub-neighbour, shift k); one species segment at a time, accumulated in a register
   {
+    const T kR = -P.EtaR * T(1.4426950408889634);
     const int nRpad = P.nR <= 16 ? 16 : 32;
     const int npl = 32 / nRpad;
     const int k = lane % nRpad, sub = lane / nRpad;
@@ -212,9 +220,10 @@ aev2_forward_row(const AevConst<T>& P, int radial_filter, const typename Vec4T<T
       const int e1 = roff[s + 1];
       if (roff[s] == e1) continue;
       T accr = T(0);
+#pragma unroll 2
       for (int e = roff[s] + sub; e < e1; e += npl) {
         const T dr = sh_r[e] - shf;
-        accr += sh_rfc[e] * t_exp(-P.EtaR * dr * dr);
+        accr += sh_rfc[e] * t_gauss(dr, kR, P.EtaR);
       }
       if (npl == 2) accr += __shfl_xor_sync(0xffffffffu, accr, 16);
       if (lane < P.nR) acc[s * P.nR + lane] = accr;
@@ -223,6 +232,7 @@ aev2_forward_row(const AevConst<T>& P, int radial_filter, const typename Vec4T<T
   // ---- angular: one species pair (s <= t) at a time; batches of 32 triples: stage 1 lane = triple, stage 2 lane = term
   {
     const int iz = lane % NZ, ia = lane / NZ;
+    const T kA = -P.EtaA * T(1.4426950408889634);
     for (int s = 0; s < P.S; s++) {
       const int as0 = min(aoff[s], capA), ns = min(aoff[s + 1], capA) - as0;
       if (ns == 0) continue;
@@ -258,16 +268,17 @@ aev2_forward_row(const AevConst<T>& P, int radial_filter, const typename Vec4T<T
             const T c = T(0.95) * (A.x * B.x + A.y * B.y + A.z * B.z);
             const T sn = t_sqrt(fmax(T(0), T(1) - c * c));
             const T fcp = T(2) * sh_afc[a] * sh_afc[b];
+            const T hc = T(0.5) * c, hs = T(0.5) * sn;
 #pragma unroll
             for (int z = 0; z < NZ; z++) {
-              const T u = fmax(T(0), T(0.5) + T(0.5) * (c * P.cosZ[z] + sn * P.sinZ[z]));
+              const T u = fmax(T(0), hc * P.cosZ[z] + (hs * P.sinZ[z] + T(0.5)));
               f1[z] = fcp * t_pow(u, P.Zeta);
             }
             const T ravg = T(0.5) * (A.w + B.w);
 #pragma unroll
             for (int q = 0; q < NA; q++) {
               const T dr = ravg - P.ShfA[q];
-              f2[q] = t_exp(-P.EtaA * dr * dr);
+              f2[q] = t_gauss(dr, kA, P.EtaA);
             }
           }
           // transposed batch buffers (idle lanes write zeros): f1T[z][lane], f2T[a][lane]; consecutive lanes -> consecutive banks
@@ -280,9 +291,22 @@ aev2_forward_row(const AevConst<T>& P, int radial_filter, const typename Vec4T<T
           if (lane < NA * NZ) {
             const V4* pa = (const V4*)(sh_f1 + iz * kAev2TS);
             const V4* pb = (const V4*)(sh_f2 + ia * kAev2TS);
-            for (int tt = 0; tt < nb4; tt++) {       // four triples per pair of vector loads
-              const V4 u = pa[tt], v = pb[tt];
-              accr += u.x * v.x + u.y * v.y + u.z * v.z + u.w * v.w;
+            if constexpr (sizeof(T) == 4) {
+              f32x2 acc2 = pk2((float)accr, 0.f);
+#pragma unroll 2
+              for (int tt = 0; tt < nb4; tt++) {     // four triples per pair of vector loads, two packed multiply-adds
+                const V4 u = pa[tt], v = pb[tt];
+                acc2 = ffma2(pk2((float)u.x, (float)u.y), pk2((float)v.x, (float)v.y), acc2);
+                acc2 = ffma2(pk2((float)u.z, (float)u.w), pk2((float)v.z, (float)v.w), acc2);
+              }
+              float lo, hi;
+              upk2(acc2, lo, hi);
+              accr = (T)(lo + hi);
+            } else {
+              for (int tt = 0; tt < nb4; tt++) {     // four triples per pair of vector loads
+                const V4 u = pa[tt], v = pb[tt];
+                accr += u.x * v.x + u.y * v.y + u.z * v.z + u.w * v.w;
+              }
             }
           }
           __syncwarp();
@@ -360,14 +384,14 @@ aev2_backward_row(const AevConst<T>& P, int radial_filter, const typename Vec4T<
   extern __shared__ __align__(32) unsigned char smem_raw[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int rstride = P.nR + 1;            // padded rows: species / species pairs land in different banks
-  constexpr int astride = NA * NZ + 1;
-  const int acc_elems = P.S * rstride + P.npairs * astride;
+  constexpr int astride = aev2_bwd_astride(NA * NZ);     // ... and a species-pair row starts on a 16-byte boundary (vector loads)
+  const int acc_elems = aev2_bwd_acc_elems(P.S, P.nR, P.npairs, NA * NZ);
   const Aev2Layout L = aev2_layout<T>(cap, capA, acc_elems, NZ, NA, true);
   unsigned char* base = smem_raw + (size_t)warp * smem_per_warp;
   V4* sh_a = (V4*)(base + L.off_a);
   V4* sh_d = (V4*)(base + L.off_d);
   T* Arad = (T*)(base + L.off_acc);
-  T* Aang = Arad + P.S * rstride;
+  T* Aang = Arad + (P.S * rstride + 3) / 4 * 4;
   T* sh_afc = (T*)(base + L.off_afc);
   T* sh_adfc = (T*)(base + L.off_adfc);
   T* sh_g = (T*)(base + L.off_g);
@@ -466,6 +490,7 @@ aev2_backward_row(const AevConst<T>& P, int radial_filter, const typename Vec4T<
   // bit 1 of rs.range_flag, which the host reports as status 3 (two atoms nearly on top of each other: the step is invalid).
   constexpr bool kFixed = sizeof(T) == 4;
   bool bad = false;
+  const T kR = -P.EtaR * T(1.4426950408889634), kA = -P.EtaA * T(1.4426950408889634), m2EtaA = T(-2) * P.EtaA;
   if (kFixed)
     for (int e = lane; e < na * 6; e += 32) sh_gi[e] = 0;
   // ---- radial: lane = neighbour
@@ -476,10 +501,11 @@ aev2_backward_row(const AevConst<T>& P, int radial_filter, const typename Vec4T<
     t_sincos(P.pi_over_Rcr * r, &sn, &cs);
     const T fc = T(0.5) * cs + T(0.5), dfc = T(-0.5) * P.pi_over_Rcr * sn;
     const T* Ar = Arad + sh_s[e] * rstride;
+    const T c2 = T(-2) * P.EtaR * fc;
     T acc = T(0);
     for (int k = 0; k < P.nR; k++) {
       const T dr = r - P.ShfR[k];
-      acc += Ar[k] * t_exp(-P.EtaR * dr * dr) * (dfc - T(2) * P.EtaR * dr * fc);
+      acc += Ar[k] * t_gauss(dr, kR, P.EtaR) * (c2 * dr + dfc);
     }
     const T coef = T(0.25) * acc / r;
     sh_g[3 * e + 0] = coef * d.x; sh_g[3 * e + 1] = coef * d.y; sh_g[3 * e + 2] = coef * d.z;
@@ -500,10 +526,11 @@ aev2_backward_row(const AevConst<T>& P, int radial_filter, const typename Vec4T<
       const T c = T(0.95) * cosv;
       const T sn = t_sqrt(fmax(T(0), T(1) - c * c));
       const T c_over_sn = c / sn;
+      const T hc = T(0.5) * c, hs = T(0.5) * sn;
       T f1[NZ], df1[NZ];
 #pragma unroll
       for (int z = 0; z < NZ; z++) {
-        const T u = fmax(T(0), T(0.5) + T(0.5) * (c * P.cosZ[z] + sn * P.sinZ[z]));
+        const T u = fmax(T(0), hc * P.cosZ[z] + (hs * P.sinZ[z] + T(0.5)));
         const T um1 = t_pow(u, P.Zeta - T(1));
         f1[z] = um1 * u;
         df1[z] = P.Zeta * um1 * T(0.5) * (P.cosZ[z] - c_over_sn * P.sinZ[z]);   // d f1 / d c
@@ -511,19 +538,51 @@ aev2_backward_row(const AevConst<T>& P, int radial_filter, const typename Vec4T<
       const T ravg = T(0.5) * (A.w + B.w);
       const T* w = Aang + P.triu[sh_as[a]][sh_as[b]] * astride;
       T S0 = T(0), S1 = T(0), S2 = T(0);
+      if constexpr (sizeof(T) == 4 && NZ % 4 == 0) {
+        // fp32: (P, Q) and (S0, S2) as packed pairs, the weights of a shift as 128-bit loads: 1.6 instructions per (q, z) term
+        // instead of 3
+        f32x2 fd[NZ];
 #pragma unroll
-      for (int q = 0; q < NA; q++) {
-        const T dr = ravg - P.ShfA[q];
-        const T f2 = t_exp(-P.EtaA * dr * dr);
-        const T df2 = T(-2) * P.EtaA * dr * f2;
-        T Pz = T(0), Qz = T(0);
+        for (int z = 0; z < NZ; z++) fd[z] = pk2((float)f1[z], (float)df1[z]);
+        f32x2 S02 = pk2(0.f, 0.f);
+        const float4* w4 = reinterpret_cast<const float4*>(w);
 #pragma unroll
-        for (int z = 0; z < NZ; z++) {
-          const T wv = w[q * NZ + z];
-          Pz += wv * f1[z];
-          Qz += wv * df1[z];
+        for (int q = 0; q < NA; q++) {
+          const float dr = (float)ravg - (float)P.ShfA[q];
+          const float f2 = t_gauss(dr, (float)kA, 0.f);
+          const float df2 = (float)m2EtaA * dr * f2;
+          f32x2 PQ = pk2(0.f, 0.f);
+#pragma unroll
+          for (int z4 = 0; z4 < NZ / 4; z4++) {
+            const float4 wq = w4[q * (NZ / 4) + z4];
+            PQ = ffma2(fd[4 * z4 + 0], pk2(wq.x, wq.x), PQ);
+            PQ = ffma2(fd[4 * z4 + 1], pk2(wq.y, wq.y), PQ);
+            PQ = ffma2(fd[4 * z4 + 2], pk2(wq.z, wq.z), PQ);
+            PQ = ffma2(fd[4 * z4 + 3], pk2(wq.w, wq.w), PQ);
+          }
+          S02 = ffma2(PQ, pk2(f2, f2), S02);
+          float Pz, Qz;
+          upk2(PQ, Pz, Qz);
+          S1 += (T)(Pz * df2);
         }
-        S0 += Pz * f2; S1 += Pz * df2; S2 += Qz * f2;
+        float s0, s2;
+        upk2(S02, s0, s2);
+        S0 = (T)s0; S2 = (T)s2;
+      } else {
+#pragma unroll
+        for (int q = 0; q < NA; q++) {
+          const T dr = ravg - P.ShfA[q];
+          const T f2 = t_gauss(dr, kA, P.EtaA);
+          const T df2 = m2EtaA * dr * f2;
+          T Pz = T(0), Qz = T(0);
+#pragma unroll
+          for (int z = 0; z < NZ; z++) {
+            const T wv = w[q * NZ + z];
+            Pz += wv * f1[z];
+            Qz += wv * df1[z];
+          }
+          S0 += Pz * f2; S1 += Pz * df2; S2 += Qz * f2;
+        }
       }
       const T half_s1 = fca * fcb * S1;                                  // 2 * fca fcb * 0.5 * S1
       const T dE_dra = T(2) * sh_adfc[a] * fcb * S0 + half_s1;

@@ -708,14 +708,15 @@ struct Engine : EngineBase {
         return 0;
       };
       auto launch2 = [&](auto kern, auto kern_strided) -> int {
-        const Aev2Layout L2 = aev2_layout<T>(cap, capA, acc_b, P.nZ, P.nA, true);
+        const int acc_b2 = aev2_bwd_acc_elems(P.S, P.nR, P.npairs, P.ang_sub);
+        const Aev2Layout L2 = aev2_layout<T>(cap, capA, acc_b2, P.nZ, P.nA, true);
         const int smem2 = L2.bytes * kAev2Warps;
         ANIB_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem2));
         const int grid = (nlocal + kAev2Warps - 1) / kAev2Warps;
         Aev2Rows rs;
         rs.range_flag = d_err.as<int>() + 1;
         if (two_pass) {
-          const Aev2Layout L1 = aev2_layout<T>(cap1, capA1, acc_b, P.nZ, P.nA, true);
+          const Aev2Layout L1 = aev2_layout<T>(cap1, capA1, acc_b2, P.nZ, P.nA, true);
           rs.ovf_cnt = d_ovf.as<int>() + 3; rs.ovf_rows = d_ovf_rows.as<int>() + nlocal;
           kern<<<grid, kAev2Warps * 32, L1.bytes * kAev2Warps, st>>>(
               P, c->use_cuaev ? 1 : 0, d_x4.as<V4>(), d_beg.as<int64_t>(), d_cnt.as<int>(), jl(), d_order.as<int>(),
