@@ -396,7 +396,8 @@ def main():
         torch.cuda.synchronize()
         rebuild_host_ms = (time.perf_counter() - t0) * 1e3
     else:
-        ani.build_neighbors(sub.species, None, nlocal, domain_list_cutoff(), lo=lo_bb, hi=hi_bb, x_dev_ptr=step.x.data_ptr())   # allocations
+        for _ in range(2):   # allocations: the first build counts and fills, the following ones write rows of a fixed stride in one pass
+            ani.build_neighbors(sub.species, None, nlocal, domain_list_cutoff(), lo=lo_bb, hi=hi_bb, x_dev_ptr=step.x.data_ptr())
         torch.cuda.synchronize()
         t0 = time.perf_counter()
         npairs_dev = ani.build_neighbors(sub.species, None, nlocal, domain_list_cutoff(), lo=lo_bb, hi=hi_bb, x_dev_ptr=step.x.data_ptr())

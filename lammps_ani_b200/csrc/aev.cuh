@@ -47,21 +47,6 @@ __device__ __forceinline__ double t_pow(double u, double p) { return u > 0.0 ? p
 __device__ __forceinline__ float t_gauss(float d, float k, float) { return exp2f(d * d * k); }
 __device__ __forceinline__ double t_gauss(double d, double, double eta) { return exp(-eta * d * d); }
 
-// Packed fp32 pairs (sm_100: FFMA2 / FMUL2 on a 64-bit register pair, one issue slot for two lanes of arithmetic; the AEV
-// kernels are bound by instruction issue).  An operand built with pk2(w, w) is issued in the scalar-broadcast form.
-typedef unsigned long long f32x2;
-__device__ __forceinline__ f32x2 pk2(float a, float b) {
-  f32x2 r;
-  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b));
-  return r;
-}
-__device__ __forceinline__ void upk2(f32x2 r, float& a, float& b) { asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(r)); }
-__device__ __forceinline__ f32x2 ffma2(f32x2 a, f32x2 b, f32x2 c) {
-  f32x2 d;
-  asm("fma.rn.ftz.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
-  return d;
-}
-
 // round-to-nearest TF32 (10-bit mantissa) kept in an fp32 container: exactly representable for tcgen05 kind::tf32
 __device__ __forceinline__ float round_tf32(float f) {
   uint32_t u;

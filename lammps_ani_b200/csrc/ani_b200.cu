@@ -5,6 +5,7 @@
 // work buffers resident in HBM; per step: pack coordinates -> AEV forward -> per-species ensemble MLP forward
 // + dE/dAEV backward -> AEV backward / force + virial scatter -> energy reduction.
 #include <algorithm>
+#include <chrono>
 #include <cmath>
 #include <cstdlib>
 #include <cstring>
@@ -118,7 +119,8 @@ struct EngineBase {
   // csr_dev_maxnn >= 0: beg_h / cnt_h are DEVICE arrays (already the engine's own d_beg / d_cnt or to be copied device to device)
   // and the value is the longest row; < 0: host arrays
   virtual int set_neighbors(int nlocal, int ntotal, const int* species_h, const int64_t* beg_h, const int* cnt_h,
-                            const int* jlist, int64_t npairs, bool jlist_on_device, int csr_dev_maxnn = -1) = 0;
+                            const int* jlist, int64_t npairs, bool jlist_on_device, int csr_dev_maxnn = -1,
+                            bool bucketed_on_device = false) = 0;
   virtual int compute(const void* x, bool x_on_device, bool x_is_float, double* out_energy, double* out_force_host,
                       void* f_dev, bool f_is_float, double* out_eatom_host, double* eatom_dev, double* out_virial9) = 0;
   virtual int get_aev(double* aev, double* daev) = 0;
@@ -355,10 +357,13 @@ struct Engine : EngineBase {
 
   // ---------------------------------------------------------------------------------------------- rebuild
   int set_neighbors(int nlocal_, int ntotal_, const int* species_h, const int64_t* beg_h, const int* cnt_h,
-                    const int* jlist, int64_t npairs_, bool jlist_on_device, int csr_dev_maxnn = -1) override {
+                    const int* jlist, int64_t npairs_, bool jlist_on_device, int csr_dev_maxnn = -1,
+                    bool bucketed_on_device = false) override {
     nlocal = nlocal_; ntotal = ntotal_; npairs = npairs_;
     cudaStream_t st = c->stream;
-    // species bucketing (stable counting sort over local atoms) -- K4 of SURVEY.md 2.1, on rebuild only
+    // species bucketing (stable counting sort over local atoms) -- K4 of SURVEY.md 2.1, on rebuild only.  The device build has
+    // done it already (boff set, d_species / d_order filled: build_neighbors); a host list is bucketed here.
+    if (!bucketed_on_device) {
     boff.assign(hm.S + 1, 0);
     for (int i = 0; i < nlocal; i++) {
       int s = species_h[i];
@@ -383,6 +388,7 @@ struct Engine : EngineBase {
       std::vector<int> cur(boff.begin(), boff.end() - 1);
       for (int i = 0; i < nlocal; i++) h_order[cur[species_h[i]]++] = i;
     }
+    }
     const bool csr_dev = csr_dev_maxnn >= 0;
     int maxnn = csr_dev ? csr_dev_maxnn : 0;
     if (!csr_dev)
@@ -393,11 +399,13 @@ struct Engine : EngineBase {
     ANIB_RESERVE(d_beg, (size_t)std::max(nlocal, 1) * sizeof(int64_t));
     ANIB_RESERVE(d_cnt, (size_t)std::max(nlocal, 1) * sizeof(int));
     ANIB_RESERVE(d_order, (size_t)std::max(nlocal, 1) * sizeof(int));
-    ANIB_CUDA_OK(cudaMemcpyAsync(d_species.p, h_cspecies.data(), (size_t)ntotal * sizeof(int), cudaMemcpyHostToDevice, st));   // compact indices
+    if (!bucketed_on_device)
+      ANIB_CUDA_OK(cudaMemcpyAsync(d_species.p, h_cspecies.data(), (size_t)ntotal * sizeof(int), cudaMemcpyHostToDevice, st));   // compact indices
     const cudaMemcpyKind ck = csr_dev ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
     ANIB_CUDA_OK(cudaMemcpyAsync(d_beg.p, beg_h, (size_t)nlocal * sizeof(int64_t), ck, st));
     ANIB_CUDA_OK(cudaMemcpyAsync(d_cnt.p, cnt_h, (size_t)nlocal * sizeof(int), ck, st));
-    ANIB_CUDA_OK(cudaMemcpyAsync(d_order.p, h_order.data(), (size_t)nlocal * sizeof(int), cudaMemcpyHostToDevice, st));
+    if (!bucketed_on_device)
+      ANIB_CUDA_OK(cudaMemcpyAsync(d_order.p, h_order.data(), (size_t)nlocal * sizeof(int), cudaMemcpyHostToDevice, st));
     if (jlist_on_device && csr_dev) {
       jlist_ext = jlist;                          // the list the device build just wrote stays where it is (no 600 MB copy)
     } else {
@@ -419,7 +427,7 @@ struct Engine : EngineBase {
   }
 
   // ---------------------------------------------------------------------------------------------- device neighbour build
-  DevBuf nb_x, nb_cell, nb_atom, nb_cell_s, nb_atom_s, nb_cbeg, nb_cend, nb_cnt, nb_beg, nb_jlist, nb_tmp;
+  DevBuf nb_x, nb_xs, nb_spec, nb_cell, nb_atom, nb_cell_s, nb_atom_s, nb_cbeg, nb_cend, nb_cnt, nb_beg, nb_jlist, nb_tmp;
   int build_neighbors(int nlocal_, int ntotal_, const int* species_h, const double* x, bool x_on_device, double cutoff,
                       const double* lo, const double* hi, int64_t* npairs_out) override {
     cudaStream_t st = c->stream;
@@ -448,7 +456,21 @@ struct Engine : EngineBase {
     ANIB_RESERVE(nb_cnt, (size_t)std::max(nlocal_, 1) * 4); ANIB_RESERVE(nb_beg, (size_t)std::max(nlocal_, 1) * 8);
     int64_t P = 0;
     int maxnn = 0;
+    bool bucketed = false;
+    static const bool nbprof = f16::env_int("ANI_B200_NB_PROF", 0) != 0;
+    auto tnow = [] { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
+    double tp[6] = {0, 0, 0, 0, 0, 0};
+    if (nbprof) { cudaStreamSynchronize(st); tp[0] = tnow(); }
     if (ntotal_ > 0 && nlocal_ > 0) {
+      // species of all atoms to the device; histogram / present set / range check there (read back with the two list scalars)
+      ANIB_RESERVE(nb_spec, (size_t)nt * 4);
+      ANIB_RESERVE(d_species, (size_t)nt * sizeof(int));
+      ANIB_RESERVE(d_order, (size_t)std::max(nlocal_, 1) * sizeof(int));
+      ANIB_RESERVE(nb_red, 64);
+      ANIB_CUDA_OK(cudaMemcpyAsync(nb_spec.p, species_h, (size_t)ntotal_ * 4, cudaMemcpyHostToDevice, st));
+      ANIB_CUDA_OK(cudaMemsetAsync(nb_red.p, 0, 64, st));
+      nb_species_stats_kernel<<<std::min(592, (ntotal_ + 255) / 256), 256, 0, st>>>(nb_spec.as<int>(), nlocal_, ntotal_, hm.S,
+                                                                                  (int*)((char*)nb_red.p + 16));
       nb_cell_id_kernel<<<(ntotal_ + 255) / 256, 256, 0, st>>>(xd, ntotal_, G, nb_cell.as<int>(), nb_atom.as<int>());
       size_t tmp_bytes = 0, scan_bytes = 0, max_bytes = 0;
       int bits = 1;
@@ -457,45 +479,128 @@ struct Engine : EngineBase {
                                       ntotal_, 0, bits, st);
       auto cnt64 = thrust::make_transform_iterator((const int*)nb_cnt.as<int>(), NbToI64());
       cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, cnt64, nb_beg.as<int64_t>(), nlocal_, st);
-      ANIB_RESERVE(nb_red, 16);
       cub::DeviceReduce::Max(nullptr, max_bytes, nb_cnt.as<int>(), (int*)nb_red.p, nlocal_, st);
-      tmp_bytes = std::max(tmp_bytes, std::max(scan_bytes, max_bytes));
+      size_t order_bytes = 0, sum_bytes = 0;
+      cub::DeviceReduce::Sum(nullptr, sum_bytes, cnt64, (int64_t*)nullptr, nlocal_, st);
+      max_bytes = std::max(max_bytes, sum_bytes);
+      int sbits = 1;
+      while ((1 << sbits) < hm.S) sbits++;
+      cub::DeviceRadixSort::SortPairs(nullptr, order_bytes, nb_spec.as<int>(), nb_cell.as<int>(), nb_atom.as<int>(), d_order.as<int>(),
+                                      nlocal_, 0, sbits, st);
+      tmp_bytes = std::max(std::max(tmp_bytes, order_bytes), std::max(scan_bytes, max_bytes));
       ANIB_RESERVE(nb_tmp, tmp_bytes + 16);
       ANIB_CUDA_OK(cub::DeviceRadixSort::SortPairs(nb_tmp.p, tmp_bytes, nb_cell.as<int>(), nb_cell_s.as<int>(), nb_atom.as<int>(),
                                                    nb_atom_s.as<int>(), ntotal_, 0, bits, st));
       ANIB_CUDA_OK(cudaMemsetAsync(nb_cbeg.p, 0, (size_t)ncell * 4, st));
       ANIB_CUDA_OK(cudaMemsetAsync(nb_cend.p, 0, (size_t)ncell * 4, st));
       nb_cell_range_kernel<<<(ntotal_ + 255) / 256, 256, 0, st>>>(nb_cell_s.as<int>(), ntotal_, nb_cbeg.as<int>(), nb_cend.as<int>());
-      nb_search_kernel<false><<<(nlocal_ + 127) / 128, 128, 0, st>>>(xd, nlocal_, G, nb_cbeg.as<int>(), nb_cend.as<int>(),
-                                                                   nb_atom_s.as<int>(), cutoff * cutoff, nb_cnt.as<int>(), nullptr, nullptr);
-      // CSR offsets, the total and the longest row on the device; only two scalars come back to the host
-      ANIB_CUDA_OK(cub::DeviceScan::ExclusiveSum(nb_tmp.p, tmp_bytes, cnt64, nb_beg.as<int64_t>(), nlocal_, st));
+      ANIB_RESERVE(nb_xs, (size_t)nt * (3 * sizeof(double) + sizeof(float4)));
+      float4* const pk = nb_xs.as<float4>();                // (x, y, z relative to the grid origin, atom index) in sorted order
+      double* const sx = (double*)(pk + nt);
+      double* const sy = sx + nt;
+      double* const sz = sy + nt;
+      nb_gather_sorted_kernel<<<(ntotal_ + 255) / 256, 256, 0, st>>>(xd, nb_atom_s.as<int>(), ntotal_, G, sx, sy, sz, pk);
+      // fp32 error bound of a squared distance near the cutoff: each relative coordinate is off by at most half an ulp of the
+      // grid extent (plus the clamped atoms just outside it: one more cell), a difference by twice that, d^2 by 2 |d| sqrt(3)
+      // times that; an order of magnitude of margin on top
+      double extent = 0.0;
+      for (int d = 0; d < 3; d++) extent = std::max(extent, hi[d] - lo[d] + 2.0 * cutoff);
+      const float eps = (float)(64.0 * cutoff * extent * 5.960464477539063e-08 + 1e-5 * cutoff * cutoff);
+      const unsigned search_grid = (unsigned)(((size_t)ntotal_ * 32 + 255) / 256);        // one warp per atom, local or ghost
+      // One pass when the longest row of the previous build is known: rows of that length plus a margin, counted and written
+      // together.  Otherwise (first build, or a row outgrew the stride) count, scan, fill.
+      int stride = nb_stride;
+      if (stride > 0 && (size_t)nlocal_ * stride * 4 > ((size_t)8 << 30)) stride = 0;     // keep the padded list under 8 GB
+      if (stride > 0) {
+        ANIB_RESERVE(nb_jlist, (size_t)nlocal_ * stride * 4);
+        nb_strided_beg_kernel<<<(nlocal_ + 255) / 256, 256, 0, st>>>(nb_beg.as<int64_t>(), nlocal_, stride);
+        nb_search_warp_kernel<2><<<search_grid, 256, 0, st>>>(sx, sy, sz, pk, ntotal_, nlocal_, G, nb_cbeg.as<int>(), nb_cend.as<int>(),
+                                                              cutoff * cutoff, eps, nb_cnt.as<int>(), nullptr, stride, nb_jlist.as<int>());
+        ANIB_CUDA_OK(cub::DeviceReduce::Sum(nb_tmp.p, tmp_bytes, cnt64, (int64_t*)((char*)nb_red.p + 8), nlocal_, st));
+      } else {
+        nb_search_warp_kernel<0><<<search_grid, 256, 0, st>>>(sx, sy, sz, pk, ntotal_, nlocal_, G, nb_cbeg.as<int>(), nb_cend.as<int>(),
+                                                              cutoff * cutoff, eps, nb_cnt.as<int>(), nullptr, 0, nullptr);
+        // CSR offsets and the total on the device
+        ANIB_CUDA_OK(cub::DeviceScan::ExclusiveSum(nb_tmp.p, tmp_bytes, cnt64, nb_beg.as<int64_t>(), nlocal_, st));
+        nb_total_kernel<<<1, 1, 0, st>>>(nb_beg.as<int64_t>(), nb_cnt.as<int>(), nlocal_, (int64_t*)((char*)nb_red.p + 8));
+      }
       ANIB_CUDA_OK(cub::DeviceReduce::Max(nb_tmp.p, tmp_bytes, nb_cnt.as<int>(), (int*)nb_red.p, nlocal_, st));
-      nb_total_kernel<<<1, 1, 0, st>>>(nb_beg.as<int64_t>(), nb_cnt.as<int>(), nlocal_, (int64_t*)((char*)nb_red.p + 8));
-      ANIB_RESERVE(h_nb, 16);
-      ANIB_CUDA_OK(cudaMemcpyAsync(h_nb.p, nb_red.p, 16, cudaMemcpyDeviceToHost, st));
+      ANIB_RESERVE(h_nb, 64);
+      if (nbprof) tp[1] = tnow();
+      ANIB_CUDA_OK(cudaMemcpyAsync(h_nb.p, nb_red.p, 64, cudaMemcpyDeviceToHost, st));       // longest row, total, species statistics
       ANIB_CUDA_OK(cudaStreamSynchronize(st));
+      if (nbprof) tp[2] = tnow();
+      if (stride > 0 && *(const int*)h_nb.p > stride) {      // a row did not fit: this build goes the two-pass way
+        stride = 0;
+        ANIB_CUDA_OK(cub::DeviceScan::ExclusiveSum(nb_tmp.p, tmp_bytes, cnt64, nb_beg.as<int64_t>(), nlocal_, st));
+      }
       maxnn = *(const int*)h_nb.p;
       P = *(const int64_t*)((const char*)h_nb.p + 8);
-      ANIB_RESERVE(nb_jlist, (size_t)std::max<int64_t>(P, 1) * 4);
-      nb_search_kernel<true><<<(nlocal_ + 127) / 128, 128, 0, st>>>(xd, nlocal_, G, nb_cbeg.as<int>(), nb_cend.as<int>(),
-                                                                  nb_atom_s.as<int>(), cutoff * cutoff, nullptr, nb_beg.as<int64_t>(),
-                                                                  nb_jlist.as<int>());
+      {
+        const int* stats = (const int*)((const char*)h_nb.p + 16);
+        if (stats[9]) { set_error("an atom has a species index outside the model's species"); return 1; }
+        boff.assign(hm.S + 1, 0);
+        for (int q = 0; q < hm.S; q++) boff[q + 1] = boff[q] + stats[q];
+        uint32_t present = (uint32_t)stats[8];
+        if (dense_aev) present = (1u << hm.S) - 1u;
+        if (present == 0) present = 1u;
+        if ((present & ~active_mask) != 0)
+          if (int rc = set_active(active_mask | present)) return rc;
+        NbSpeciesMap sm;
+        for (int q = 0; q < 8; q++) sm.cmap[q] = q < hm.S ? cmap[q] : -1;
+        nb_species_compact_kernel<<<(ntotal_ + 255) / 256, 256, 0, st>>>(nb_spec.as<int>(), ntotal_, sm, d_species.as<int>());
+        // row order = local atoms bucketed by species, atom order kept inside a bucket: a stable sort of (species, index);
+        // nb_atom still holds 0, 1, 2, ... and the unsorted cell ids in nb_cell are no longer needed
+        ANIB_CUDA_OK(cub::DeviceRadixSort::SortPairs(nb_tmp.p, tmp_bytes, nb_spec.as<int>(), nb_cell.as<int>(), nb_atom.as<int>(),
+                                                     d_order.as<int>(), nlocal_, 0, sbits, st));
+        bucketed = true;
+      }
+      if (stride == 0) {
+        ANIB_RESERVE(nb_jlist, (size_t)std::max<int64_t>(P, 1) * 4);
+        nb_search_warp_kernel<1><<<search_grid, 256, 0, st>>>(sx, sy, sz, pk, ntotal_, nlocal_, G, nb_cbeg.as<int>(), nb_cend.as<int>(),
+                                                              cutoff * cutoff, eps, nullptr, nb_beg.as<int64_t>(), 0, nb_jlist.as<int>());
+      }
+      nb_rows_strided = stride > 0;
+      nb_stride = (maxnn + maxnn / 8 + 8 + 7) / 8 * 8;       // rows of the next build
       ANIB_CUDA_OK(cudaGetLastError());
-      c->launches = 7;
+      c->launches = 11;
     }
     if (npairs_out) *npairs_out = P;
-    return set_neighbors(nlocal_, ntotal_, species_h, nb_beg.as<int64_t>(), nb_cnt.as<int>(), nb_jlist.as<int>(), P, true, maxnn);
+    if (nbprof) { tp[3] = tnow(); cudaStreamSynchronize(st); tp[4] = tnow(); }
+    const int rc = set_neighbors(nlocal_, ntotal_, species_h, nb_beg.as<int64_t>(), nb_cnt.as<int>(), nb_jlist.as<int>(), P, true, maxnn, bucketed);
+    if (nbprof) {
+      tp[5] = tnow();
+      fprintf(stderr, "[nb prof] enqueue (species H2D, sort, search) %.3f ms | wait for it %.3f | enqueue the rest %.3f | done %.3f | "
+                      "set_neighbors %.3f | total %.3f ms\n", tp[1] - tp[0], tp[2] - tp[1], tp[3] - tp[2], tp[4] - tp[3], tp[5] - tp[4], tp[5] - tp[0]);
+    }
+    return rc;
   }
   DevBuf nb_red;
   PinnedBuf h_nb;
+  int nb_stride = 0;              // row stride for the one-pass build (0: unknown yet)
+  bool nb_rows_strided = false;   // the installed device-built list has padded rows
 
   void release_pins() override { pin_x.release(); pin_f.release(); }
 
   int get_neighbors(int* numneigh, int* jlist) override {
     ANIB_CUDA_OK(cudaStreamSynchronize(c->stream));
     if (numneigh && nlocal > 0) ANIB_CUDA_OK(cudaMemcpy(numneigh, d_cnt.p, (size_t)nlocal * 4, cudaMemcpyDeviceToHost));
-    if (jlist && npairs > 0) ANIB_CUDA_OK(cudaMemcpy(jlist, jl(), (size_t)npairs * 4, cudaMemcpyDeviceToHost));
+    if (jlist && npairs > 0) {
+      if (jlist_ext && nb_rows_strided) {                    // padded rows: copy row by row segments through the CSR offsets
+        std::vector<int64_t> hb(nlocal);
+        std::vector<int> hc(nlocal);
+        ANIB_CUDA_OK(cudaMemcpy(hb.data(), d_beg.p, (size_t)nlocal * 8, cudaMemcpyDeviceToHost));
+        ANIB_CUDA_OK(cudaMemcpy(hc.data(), d_cnt.p, (size_t)nlocal * 4, cudaMemcpyDeviceToHost));
+        const int64_t span = nlocal > 0 ? hb[nlocal - 1] + hc[nlocal - 1] : 0;
+        std::vector<int> all((size_t)std::max<int64_t>(span, 1));
+        ANIB_CUDA_OK(cudaMemcpy(all.data(), jl(), (size_t)span * 4, cudaMemcpyDeviceToHost));
+        int64_t p = 0;
+        for (int i = 0; i < nlocal; i++)
+          for (int q = 0; q < hc[i]; q++) jlist[p++] = all[(size_t)hb[i] + q];
+      } else {
+        ANIB_CUDA_OK(cudaMemcpy(jlist, jl(), (size_t)npairs * 4, cudaMemcpyDeviceToHost));
+      }
+    }
     return 0;
   }
 
@@ -869,6 +974,8 @@ struct Engine : EngineBase {
     ANIB_CUDA_OK(cudaStreamSynchronize(c->stream));
     std::vector<T> tmp((size_t)nlocal * ld_aev);
     const int Lf = Pfull.aev_len;
+    h_order.resize(nlocal);                   // (the device build leaves the row order on the device only)
+    if (nlocal > 0) ANIB_CUDA_OK(cudaMemcpy(h_order.data(), d_order.p, (size_t)nlocal * sizeof(int), cudaMemcpyDeviceToHost));
     for (int pass = 0; pass < 2; pass++) {
       double* out = pass == 0 ? aev : daev;
       if (!out) continue;
