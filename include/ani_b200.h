@@ -194,6 +194,15 @@ int ani_halo_plan_create(ani_ctx* ctx, const char unique_id[128], int nranks, in
 void ani_halo_plan_destroy(ani_halo_plan* plan);
 int ani_halo_forward(ani_halo_plan* plan, double* x_dev);
 int ani_halo_reverse(ani_halo_plan* plan, double* f_dev);
+/* One domain-decomposed step in one call: ani_halo_forward(x), ani_compute_device(x, f), ani_halo_reverse(f), with x / f the
+ * caller's device arrays of doubles [ntotal][3] (f cleared by the caller: Verlet::force_clear).  What the single call adds:
+ * when the neighbour list was built on the device (ani_build_neighbors records which local atoms have a ghost neighbour), the
+ * exchange runs on a second stream under the INTERIOR atoms' share of the AEV kernels -- their rows read no ghost position and
+ * produce no ghost force -- instead of in front of and behind the step (comm_brick.cpp:538-593,1023-1053 are serial in the
+ * reference; KOKKOS overlaps nothing either).  ani_ctx_set_option(ctx, "halo_overlap", 0) serialises it again; a host-installed
+ * list always runs serialised.  The context's stream sees the step complete, ghost forces folded, when the call returns. */
+int ani_compute_device_halo(ani_ctx* ctx, ani_halo_plan* plan, double* x_dev, double* f_dev, double* eatom_dev,
+                            double* out_energy, double* out_virial9);
 
 /* Device-memory helpers on the context's device and stream, for callers that do not link the CUDA runtime (the LAMMPS
  * plugin's device-resident mode): alloc / free, blocking upload / download ordered after everything queued on the context's

@@ -114,6 +114,59 @@ struct UserPin {
   ~UserPin() { release(); }
 };
 
+// ---- ghost exchange pieces (ani_halo_forward / ani_halo_reverse, and the overlapped exchange inside Engine::compute), on a given stream
+static int halo_forward_on(HaloPlan& p, double* x_dev, cudaStream_t st) {
+  if (p.nsend > 0) {
+    halo_pack_kernel<double><<<(unsigned)((p.nsend * 3 + 255) / 256), 256, 0, st>>>(x_dev, p.d_send_index, p.d_send_shift, p.nsend, p.d_send_buf);
+    ANIB_CUDA_OK(cudaGetLastError());
+  }
+  double* ghosts = x_dev + (size_t)p.nlocal * 3;
+  const int64_t self = p.send_off[p.rank + 1] - p.send_off[p.rank];
+  if (self > 0)       // periodic self images: a device copy, no communication
+    ANIB_CUDA_OK(cudaMemcpyAsync(ghosts + p.recv_off[p.rank] * 3, p.d_send_buf + p.send_off[p.rank] * 3, (size_t)self * 3 * sizeof(double),
+                                 cudaMemcpyDeviceToDevice, st));
+  if (p.nranks > 1) {
+    NcclApi& n = nccl_api();
+    ANIB_NCCL_OK(n.GroupStart());
+    for (int r = 0; r < p.nranks; r++) {
+      if (r == p.rank) continue;
+      const int64_t ns = p.send_off[r + 1] - p.send_off[r], nr = p.recv_off[r + 1] - p.recv_off[r];
+      if (ns > 0) ANIB_NCCL_OK(n.Send(p.d_send_buf + p.send_off[r] * 3, (size_t)ns * 3, ncclDouble, r, p.comm, st));
+      if (nr > 0) ANIB_NCCL_OK(n.Recv(ghosts + p.recv_off[r] * 3, (size_t)nr * 3, ncclDouble, r, p.comm, st));
+    }
+    ANIB_NCCL_OK(n.GroupEnd());
+  }
+  return 0;
+}
+// ghost forces back to their owners' send buffers ...
+static int halo_reverse_exchange_on(HaloPlan& p, double* f_dev, cudaStream_t st) {
+  double* ghosts = f_dev + (size_t)p.nlocal * 3;
+  const int64_t self = p.send_off[p.rank + 1] - p.send_off[p.rank];
+  if (self > 0)
+    ANIB_CUDA_OK(cudaMemcpyAsync(p.d_send_buf + p.send_off[p.rank] * 3, ghosts + p.recv_off[p.rank] * 3, (size_t)self * 3 * sizeof(double),
+                                 cudaMemcpyDeviceToDevice, st));
+  if (p.nranks > 1) {
+    NcclApi& n = nccl_api();
+    ANIB_NCCL_OK(n.GroupStart());
+    for (int r = 0; r < p.nranks; r++) {
+      if (r == p.rank) continue;
+      const int64_t ns = p.send_off[r + 1] - p.send_off[r], nr = p.recv_off[r + 1] - p.recv_off[r];
+      if (nr > 0) ANIB_NCCL_OK(n.Send(ghosts + p.recv_off[r] * 3, (size_t)nr * 3, ncclDouble, r, p.comm, st));
+      if (ns > 0) ANIB_NCCL_OK(n.Recv(p.d_send_buf + p.send_off[r] * 3, (size_t)ns * 3, ncclDouble, r, p.comm, st));
+    }
+    ANIB_NCCL_OK(n.GroupEnd());
+  }
+  return 0;
+}
+// ... and f[owner] += what came back (newton off: the pair style folds its own ghost forces, pair_ani.cpp:197-201)
+static int halo_reverse_unpack_on(HaloPlan& p, double* f_dev, cudaStream_t st) {
+  if (p.nsend > 0) {
+    halo_unpack_add_kernel<double><<<(unsigned)((p.nsend * 3 + 255) / 256), 256, 0, st>>>(f_dev, p.d_send_index, p.d_send_buf, p.nsend);
+    ANIB_CUDA_OK(cudaGetLastError());
+  }
+  return 0;
+}
+
 struct EngineBase {
   virtual ~EngineBase() {}
   // csr_dev_maxnn >= 0: beg_h / cnt_h are DEVICE arrays (already the engine's own d_beg / d_cnt or to be copied device to device)
@@ -122,7 +175,8 @@ struct EngineBase {
                             const int* jlist, int64_t npairs, bool jlist_on_device, int csr_dev_maxnn = -1,
                             bool bucketed_on_device = false) = 0;
   virtual int compute(const void* x, bool x_on_device, bool x_is_float, double* out_energy, double* out_force_host,
-                      void* f_dev, bool f_is_float, double* out_eatom_host, double* eatom_dev, double* out_virial9) = 0;
+                      void* f_dev, bool f_is_float, double* out_eatom_host, double* eatom_dev, double* out_virial9,
+                      HaloPlan* halo = nullptr) = 0;
   virtual int get_aev(double* aev, double* daev) = 0;
   virtual int build_neighbors(int nlocal, int ntotal, const int* species_h, const double* x, bool x_on_device, double cutoff,
                               const double* lo, const double* hi, int64_t* npairs_out) = 0;
@@ -175,6 +229,9 @@ struct ani_ctx {
   std::vector<int> h_jl;
   // caller arrays page-locked on request (ani_ctx_pin_host), released by ani_ctx_release_host_buffers / destroy
   std::vector<void*> pinned_host;
+  cudaStream_t comm_stream = nullptr;        // second stream + events of the overlapped ghost exchange (Engine::compute)
+  cudaEvent_t evh[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+  int opt_halo_overlap = 1;
   unsigned long long* d_word = nullptr;      // one device word + its pinned host mirror (ani_md_max_disp2)
   unsigned long long* h_word = nullptr;
 };
@@ -364,6 +421,7 @@ struct Engine : EngineBase {
     // species bucketing (stable counting sort over local atoms) -- K4 of SURVEY.md 2.1, on rebuild only.  The device build has
     // done it already (boff set, d_species / d_order filled: build_neighbors); a host list is bucketed here.
     if (!bucketed_on_device) {
+    rows_int = -1;                                   // a host list comes without the interior / boundary split
     boff.assign(hm.S + 1, 0);
     for (int i = 0; i < nlocal; i++) {
       int s = species_h[i];
@@ -427,7 +485,7 @@ struct Engine : EngineBase {
   }
 
   // ---------------------------------------------------------------------------------------------- device neighbour build
-  DevBuf nb_x, nb_xs, nb_spec, nb_cell, nb_atom, nb_cell_s, nb_atom_s, nb_cbeg, nb_cend, nb_cnt, nb_beg, nb_jlist, nb_tmp;
+  DevBuf nb_x, nb_xs, nb_spec, nb_bnd, nb_key, d_rows, d_sel, nb_cell, nb_atom, nb_cell_s, nb_atom_s, nb_cbeg, nb_cend, nb_cnt, nb_beg, nb_jlist, nb_tmp;
   int build_neighbors(int nlocal_, int ntotal_, const int* species_h, const double* x, bool x_on_device, double cutoff,
                       const double* lo, const double* hi, int64_t* npairs_out) override {
     cudaStream_t st = c->stream;
@@ -466,11 +524,12 @@ struct Engine : EngineBase {
       ANIB_RESERVE(nb_spec, (size_t)nt * 4);
       ANIB_RESERVE(d_species, (size_t)nt * sizeof(int));
       ANIB_RESERVE(d_order, (size_t)std::max(nlocal_, 1) * sizeof(int));
-      ANIB_RESERVE(nb_red, 64);
+      ANIB_RESERVE(nb_red, 128);
+      ANIB_RESERVE(nb_bnd, (size_t)std::max(nlocal_, 1) * 4);
+      ANIB_RESERVE(nb_key, (size_t)std::max(nlocal_, 1) * 4);
+      ANIB_RESERVE(d_rows, (size_t)std::max(nlocal_, 1) * 4);
       ANIB_CUDA_OK(cudaMemcpyAsync(nb_spec.p, species_h, (size_t)ntotal_ * 4, cudaMemcpyHostToDevice, st));
-      ANIB_CUDA_OK(cudaMemsetAsync(nb_red.p, 0, 64, st));
-      nb_species_stats_kernel<<<std::min(592, (ntotal_ + 255) / 256), 256, 0, st>>>(nb_spec.as<int>(), nlocal_, ntotal_, hm.S,
-                                                                                  (int*)((char*)nb_red.p + 16));
+      ANIB_CUDA_OK(cudaMemsetAsync(nb_red.p, 0, 128, st));
       nb_cell_id_kernel<<<(ntotal_ + 255) / 256, 256, 0, st>>>(xd, ntotal_, G, nb_cell.as<int>(), nb_atom.as<int>());
       size_t tmp_bytes = 0, scan_bytes = 0, max_bytes = 0;
       int bits = 1;
@@ -485,7 +544,8 @@ struct Engine : EngineBase {
       max_bytes = std::max(max_bytes, sum_bytes);
       int sbits = 1;
       while ((1 << sbits) < hm.S) sbits++;
-      cub::DeviceRadixSort::SortPairs(nullptr, order_bytes, nb_spec.as<int>(), nb_cell.as<int>(), nb_atom.as<int>(), d_order.as<int>(),
+      sbits++;                                              // the key is 2 * species + boundary flag
+      cub::DeviceRadixSort::SortPairs(nullptr, order_bytes, nb_key.as<int>(), nb_cell.as<int>(), nb_atom.as<int>(), d_order.as<int>(),
                                       nlocal_, 0, sbits, st);
       tmp_bytes = std::max(std::max(tmp_bytes, order_bytes), std::max(scan_bytes, max_bytes));
       ANIB_RESERVE(nb_tmp, tmp_bytes + 16);
@@ -515,19 +575,22 @@ struct Engine : EngineBase {
         ANIB_RESERVE(nb_jlist, (size_t)nlocal_ * stride * 4);
         nb_strided_beg_kernel<<<(nlocal_ + 255) / 256, 256, 0, st>>>(nb_beg.as<int64_t>(), nlocal_, stride);
         nb_search_warp_kernel<2><<<search_grid, 256, 0, st>>>(sx, sy, sz, pk, ntotal_, nlocal_, G, nb_cbeg.as<int>(), nb_cend.as<int>(),
-                                                              cutoff * cutoff, eps, nb_cnt.as<int>(), nullptr, stride, nb_jlist.as<int>());
+                                                              cutoff * cutoff, eps, nb_cnt.as<int>(), nb_bnd.as<int>(), nullptr, stride,
+                                                              nb_jlist.as<int>());
         ANIB_CUDA_OK(cub::DeviceReduce::Sum(nb_tmp.p, tmp_bytes, cnt64, (int64_t*)((char*)nb_red.p + 8), nlocal_, st));
       } else {
         nb_search_warp_kernel<0><<<search_grid, 256, 0, st>>>(sx, sy, sz, pk, ntotal_, nlocal_, G, nb_cbeg.as<int>(), nb_cend.as<int>(),
-                                                              cutoff * cutoff, eps, nb_cnt.as<int>(), nullptr, 0, nullptr);
+                                                              cutoff * cutoff, eps, nb_cnt.as<int>(), nb_bnd.as<int>(), nullptr, 0, nullptr);
         // CSR offsets and the total on the device
         ANIB_CUDA_OK(cub::DeviceScan::ExclusiveSum(nb_tmp.p, tmp_bytes, cnt64, nb_beg.as<int64_t>(), nlocal_, st));
         nb_total_kernel<<<1, 1, 0, st>>>(nb_beg.as<int64_t>(), nb_cnt.as<int>(), nlocal_, (int64_t*)((char*)nb_red.p + 8));
       }
       ANIB_CUDA_OK(cub::DeviceReduce::Max(nb_tmp.p, tmp_bytes, nb_cnt.as<int>(), (int*)nb_red.p, nlocal_, st));
-      ANIB_RESERVE(h_nb, 64);
+      nb_species_stats_kernel<<<std::min(592, (ntotal_ + 255) / 256), 256, 0, st>>>(nb_spec.as<int>(), nb_bnd.as<int>(), nlocal_, ntotal_, hm.S,
+                                                                                  nb_key.as<int>(), (int*)((char*)nb_red.p + 16));
+      ANIB_RESERVE(h_nb, 128);
       if (nbprof) tp[1] = tnow();
-      ANIB_CUDA_OK(cudaMemcpyAsync(h_nb.p, nb_red.p, 64, cudaMemcpyDeviceToHost, st));       // longest row, total, species statistics
+      ANIB_CUDA_OK(cudaMemcpyAsync(h_nb.p, nb_red.p, 128, cudaMemcpyDeviceToHost, st));       // longest row, total, species statistics
       ANIB_CUDA_OK(cudaStreamSynchronize(st));
       if (nbprof) tp[2] = tnow();
       if (stride > 0 && *(const int*)h_nb.p > stride) {      // a row did not fit: this build goes the two-pass way
@@ -538,10 +601,21 @@ struct Engine : EngineBase {
       P = *(const int64_t*)((const char*)h_nb.p + 8);
       {
         const int* stats = (const int*)((const char*)h_nb.p + 16);
-        if (stats[9]) { set_error("an atom has a species index outside the model's species"); return 1; }
+        if (stats[17]) { set_error("an atom has a species index outside the model's species"); return 1; }
         boff.assign(hm.S + 1, 0);
-        for (int q = 0; q < hm.S; q++) boff[q + 1] = boff[q] + stats[q];
-        uint32_t present = (uint32_t)stats[8];
+        NbRowSplit sp;
+        memset(&sp, 0, sizeof(sp));
+        sp.S = hm.S;
+        int n_int = 0, n_bnd = 0;
+        for (int q = 0; q < hm.S; q++) {
+          boff[q + 1] = boff[q] + stats[2 * q] + stats[2 * q + 1];
+          sp.nint[q] = stats[2 * q]; sp.int_before[q] = n_int; sp.bnd_before[q] = n_bnd;
+          n_int += stats[2 * q]; n_bnd += stats[2 * q + 1];
+        }
+        for (int q = 0; q <= hm.S; q++) sp.boff[q] = boff[q];
+        sp.n_int = n_int;
+        rows_int = n_int; rows_bnd = n_bnd;
+        uint32_t present = (uint32_t)stats[16];
         if (dense_aev) present = (1u << hm.S) - 1u;
         if (present == 0) present = 1u;
         if ((present & ~active_mask) != 0)
@@ -551,14 +625,18 @@ struct Engine : EngineBase {
         nb_species_compact_kernel<<<(ntotal_ + 255) / 256, 256, 0, st>>>(nb_spec.as<int>(), ntotal_, sm, d_species.as<int>());
         // row order = local atoms bucketed by species, atom order kept inside a bucket: a stable sort of (species, index);
         // nb_atom still holds 0, 1, 2, ... and the unsorted cell ids in nb_cell are no longer needed
-        ANIB_CUDA_OK(cub::DeviceRadixSort::SortPairs(nb_tmp.p, tmp_bytes, nb_spec.as<int>(), nb_cell.as<int>(), nb_atom.as<int>(),
+        ANIB_CUDA_OK(cub::DeviceRadixSort::SortPairs(nb_tmp.p, tmp_bytes, nb_key.as<int>(), nb_cell.as<int>(), nb_atom.as<int>(),
                                                      d_order.as<int>(), nlocal_, 0, sbits, st));
+        nb_row_lists_kernel<<<(nlocal_ + 255) / 256, 256, 0, st>>>(sp, nlocal_, d_rows.as<int>());
+        const int hsel[2] = {n_int, n_bnd};
+        ANIB_RESERVE(d_sel, 2 * sizeof(int));
+        ANIB_CUDA_OK(cudaMemcpyAsync(d_sel.p, hsel, sizeof(hsel), cudaMemcpyHostToDevice, st));   // (staged by the runtime: hsel may go)
         bucketed = true;
       }
       if (stride == 0) {
         ANIB_RESERVE(nb_jlist, (size_t)std::max<int64_t>(P, 1) * 4);
         nb_search_warp_kernel<1><<<search_grid, 256, 0, st>>>(sx, sy, sz, pk, ntotal_, nlocal_, G, nb_cbeg.as<int>(), nb_cend.as<int>(),
-                                                              cutoff * cutoff, eps, nullptr, nb_beg.as<int64_t>(), 0, nb_jlist.as<int>());
+                                                              cutoff * cutoff, eps, nullptr, nullptr, nb_beg.as<int64_t>(), 0, nb_jlist.as<int>());
       }
       nb_rows_strided = stride > 0;
       nb_stride = (maxnn + maxnn / 8 + 8 + 7) / 8 * 8;       // rows of the next build
@@ -578,6 +656,7 @@ struct Engine : EngineBase {
   DevBuf nb_red;
   PinnedBuf h_nb;
   int nb_stride = 0;              // row stride for the one-pass build (0: unknown yet)
+  int rows_int = -1, rows_bnd = 0;   // interior / boundary rows listed in d_rows (device build); -1: no split known
   bool nb_rows_strided = false;   // the installed device-built list has padded rows
 
   void release_pins() override { pin_x.release(); pin_f.release(); }
@@ -673,7 +752,8 @@ struct Engine : EngineBase {
 
   // ---------------------------------------------------------------------------------------------- one step
   int compute(const void* x, bool x_on_device, bool x_is_float, double* out_energy, double* out_force_host, void* f_dev,
-              bool f_is_float, double* out_eatom_host, double* eatom_dev, double* out_virial9) override {
+              bool f_is_float, double* out_eatom_host, double* eatom_dev, double* out_virial9,
+              HaloPlan* halo = nullptr) override {
     cudaStream_t st = c->stream;
     c->launches = 0;
     const bool tm = c->timing;
@@ -693,11 +773,39 @@ struct Engine : EngineBase {
       x_is_float = false;
     }
     using V4 = typename Vec4T<T>::type;
-    if (ntotal > 0) {
-      pack_x_kernel<T><<<(ntotal + 255) / 256, 256, 0, st>>>(xsrc, x_is_float ? 1 : 0, d_species.as<int>(), ntotal,
-                                                             d_x4.as<V4>());
-      c->launches++;
+    // Ghost exchange of a domain-decomposed step (halo != nullptr: x and f are the caller's DEVICE arrays of doubles).  With
+    // the interior / boundary row split of a device-built list the exchange runs on a second stream and overlaps the interior
+    // atoms' share of the AEV kernels (their rows read no ghost position and give no ghost force); otherwise it is
+    // serialised in front of and behind the step.
+    const bool aev2_ok = aev_gen == 2 && ((P.nZ == 4 && P.nA == 8) || (P.nZ == 8 && P.nA == 4) || (P.nZ == 8 && P.nA == 8));
+    if (halo && (!x_on_device || x_is_float || !f_dev || f_is_float)) {
+      set_error("the ghost exchange needs device arrays of doubles for x and f");
+      return 1;
     }
+    const int nghost = ntotal - nlocal;
+    const bool overlap = halo && c->opt_halo_overlap && rows_int >= 0 && aev2_ok && nlocal > 0 && nghost > 0;
+    cudaStream_t cs = nullptr;
+    if (overlap) {
+      if (!c->comm_stream) {
+        ANIB_CUDA_OK(cudaStreamCreateWithFlags(&c->comm_stream, cudaStreamNonBlocking));
+        for (int q = 0; q < 5; q++) ANIB_CUDA_OK(cudaEventCreateWithFlags(&c->evh[q], cudaEventDisableTiming));
+      }
+      cs = c->comm_stream;
+      ANIB_CUDA_OK(cudaEventRecord(c->evh[0], st));                 // x of the local atoms is final
+      ANIB_CUDA_OK(cudaStreamWaitEvent(cs, c->evh[0], 0));
+      if (int rc = halo_forward_on(*halo, (double*)const_cast<void*>(x), cs)) return rc;
+      ANIB_CUDA_OK(cudaEventRecord(c->evh[1], cs));                 // ghost positions have arrived
+    } else if (halo) {
+      if (int rc = halo_forward_on(*halo, (double*)const_cast<void*>(x), st)) return rc;
+    }
+    auto pack_range = [&](int first, int count) {
+      if (count <= 0) return;
+      const void* src = x_is_float ? (const void*)((const float*)xsrc + (size_t)first * 3) : (const void*)((const double*)xsrc + (size_t)first * 3);
+      pack_x_kernel<T><<<(count + 255) / 256, 256, 0, st>>>(src, x_is_float ? 1 : 0, d_species.as<int>() + first, count, d_x4.as<V4>() + first);
+      c->launches++;
+    };
+    if (overlap) pack_range(0, nlocal);
+    else pack_range(0, ntotal);
     ANIB_CUDA_OK(cudaMemsetAsync(d_force.p, 0, (size_t)ntotal * 3 * sizeof(T), st));
     const bool want_virial = out_virial9 != nullptr;
     if (want_virial) ANIB_CUDA_OK(cudaMemsetAsync(d_virial.p, 0, kVirialSlots * 9 * sizeof(double), st));
@@ -718,9 +826,9 @@ struct Engine : EngineBase {
     const bool two_pass_on = c->opt_aev_two_pass != 0;
     const int cap1 = std::min(cap, cap_fit), capA1 = std::min(capA, std::max(capA_fit, 8));
     const bool two_pass = two_pass_on && aev_gen == 2 && cap_fit > 0 && nlocal > 0 && (cap1 + 16 <= cap || capA1 + 16 <= capA);
-    ANIB_RESERVE(d_ovf, 4 * sizeof(int));
-    ANIB_RESERVE(d_ovf_rows, (size_t)std::max(nlocal, 1) * 2 * sizeof(int));
-    ANIB_CUDA_OK(cudaMemsetAsync(d_ovf.p, 0, 4 * sizeof(int), st));
+    ANIB_RESERVE(d_ovf, 8 * sizeof(int));                 // [max n, max na, deferred rows: forward, backward, backward (interior)]
+    ANIB_RESERVE(d_ovf_rows, (size_t)std::max(nlocal, 1) * 3 * sizeof(int));
+    ANIB_CUDA_OK(cudaMemsetAsync(d_ovf.p, 0, 8 * sizeof(int), st));
     if (tm) cudaEventRecord(c->ev[1], st);
     // ---- (1) AEV forward
     const bool f16_mode = (sizeof(T) == 4) && c->mlp_mode == ANI_MLP_F16X3;
@@ -748,30 +856,47 @@ struct Engine : EngineBase {
       }
       auto launch2 = [&](auto kern, auto kern_strided) -> int {
         const Aev2Layout L2 = aev2_layout<T>(cap, capA, P.aev_len, P.nZ, P.nA, false);
+        const Aev2Layout L1 = aev2_layout<T>(cap1, capA1, P.aev_len, P.nZ, P.nA, false);
         const int smem2 = L2.bytes * kAev2Warps;
         ANIB_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem2));
+        ANIB_CUDA_OK(cudaFuncSetAttribute(kern_strided, cudaFuncAttributeMaxDynamicSharedMemorySize, smem2));
         const int grid = (nlocal + kAev2Warps - 1) / kAev2Warps;
+        // one launch: `direct` = every row, one per warp; otherwise the rows of a list (grid-stride).  small = the buffers that
+        // fit recent steps, rows that do not fit being deferred to the list the last launch works off with list-sized buffers
+        auto go = [&](bool direct, int g, bool small, Aev2Rows rs) {
+          const int cp = small ? cap1 : cap, cpA = small ? capA1 : capA, lb = small ? L1.bytes : L2.bytes;
+          if (direct)
+            kern<<<g, kAev2Warps * 32, lb * kAev2Warps, st>>>(
+                P, c->use_cuaev ? 1 : 0, d_x4.as<V4>(), d_beg.as<int64_t>(), d_cnt.as<int>(), jl(), d_order.as<int>(),
+                nlocal, rows, ld_aev, hi, lo, ldp, plane_mode, f16::kScaleAev, cp, cpA, lb, d_err.as<int>(), rs);
+          else
+            kern_strided<<<g, kAev2Warps * 32, lb * kAev2Warps, st>>>(
+                P, c->use_cuaev ? 1 : 0, d_x4.as<V4>(), d_beg.as<int64_t>(), d_cnt.as<int>(), jl(), d_order.as<int>(),
+                nlocal, rows, ld_aev, hi, lo, ldp, plane_mode, f16::kScaleAev, cp, cpA, lb, d_err.as<int>(), rs);
+          c->launches++;
+        };
         Aev2Rows rs;
         rs.stats = d_ovf.as<int>();
-        if (two_pass) {   // pass 1: buffers that fit recent steps; rows that do not fit are deferred
-          const Aev2Layout L1 = aev2_layout<T>(cap1, capA1, P.aev_len, P.nZ, P.nA, false);
-          rs.ovf_cnt = d_ovf.as<int>() + 2; rs.ovf_rows = d_ovf_rows.as<int>();
-          kern<<<grid, kAev2Warps * 32, L1.bytes * kAev2Warps, st>>>(
-              P, c->use_cuaev ? 1 : 0, d_x4.as<V4>(), d_beg.as<int64_t>(), d_cnt.as<int>(), jl(), d_order.as<int>(),
-              nlocal, rows, ld_aev, hi, lo, ldp, plane_mode, f16::kScaleAev, cap1, capA1, L1.bytes, d_err.as<int>(), rs);
-          c->launches++;
-          rs = Aev2Rows();
-          rs.sel_cnt = d_ovf.as<int>() + 2; rs.sel_rows = d_ovf_rows.as<int>();
+        if (two_pass) { rs.ovf_cnt = d_ovf.as<int>() + 2; rs.ovf_rows = d_ovf_rows.as<int>(); }
+        if (overlap) {
+          // interior rows while the ghost positions travel, then the ghosts' coordinates, then the boundary rows
+          Aev2Rows ri = rs;
+          ri.sel_cnt = d_sel.as<int>(); ri.sel_rows = d_rows.as<int>();
+          if (rows_int > 0) go(false, (rows_int + kAev2Warps - 1) / kAev2Warps, two_pass, ri);
+          ANIB_CUDA_OK(cudaStreamWaitEvent(st, c->evh[1], 0));
+          pack_range(nlocal, nghost);
+          Aev2Rows rb = rs;
+          rb.sel_cnt = d_sel.as<int>() + 1; rb.sel_rows = d_rows.as<int>() + rows_int;
+          if (rows_bnd > 0) go(false, (rows_bnd + kAev2Warps - 1) / kAev2Warps, two_pass, rb);
+        } else {
+          go(true, grid, two_pass, rs);
         }
-        if (two_pass) {
-          ANIB_CUDA_OK(cudaFuncSetAttribute(kern_strided, cudaFuncAttributeMaxDynamicSharedMemorySize, smem2));
-          kern_strided<<<std::min(grid, 592), kAev2Warps * 32, smem2, st>>>(
-              P, c->use_cuaev ? 1 : 0, d_x4.as<V4>(), d_beg.as<int64_t>(), d_cnt.as<int>(), jl(), d_order.as<int>(),
-              nlocal, rows, ld_aev, hi, lo, ldp, plane_mode, f16::kScaleAev, cap, capA, L2.bytes, d_err.as<int>(), rs);
-        } else
-          kern<<<grid, kAev2Warps * 32, smem2, st>>>(
-              P, c->use_cuaev ? 1 : 0, d_x4.as<V4>(), d_beg.as<int64_t>(), d_cnt.as<int>(), jl(), d_order.as<int>(),
-              nlocal, rows, ld_aev, hi, lo, ldp, plane_mode, f16::kScaleAev, cap, capA, L2.bytes, d_err.as<int>(), rs);
+        if (two_pass) {   // the deferred rows
+          Aev2Rows r2;
+          r2.sel_cnt = d_ovf.as<int>() + 2; r2.sel_rows = d_ovf_rows.as<int>();
+          go(false, std::min(grid, 592), false, r2);
+        }
+        c->launches--;    // (the caller counts the last launch)
         return 0;
       };
       int rc2 = 0;
@@ -798,6 +923,16 @@ struct Engine : EngineBase {
       if (rc) return rc;
     }
     if (tm) cudaEventRecord(c->ev[3], st);
+    const bool want_e = out_energy != nullptr;
+    // ---- (3b) RepulsionXTB pair term (models with rep_calc): forces / virial into the same arrays, energy into scalars[1]
+    // (in front of the AEV backward: with the overlapped exchange the ghost forces leave in the middle of that)
+    if (hm.use_repulsion && nlocal > 0) {
+      if (want_e) ANIB_CUDA_OK(cudaMemsetAsync(d_scalars.as<double>() + 1, 0, sizeof(double), st));
+      repulsion_kernel<T><<<(unsigned)(((int64_t)nlocal * 32 + 255) / 256), 256, 0, st>>>(
+          rep, d_x4.as<V4>(), d_beg.as<int64_t>(), d_cnt.as<int>(), jl(), nlocal, d_force.as<T>(),
+          want_virial ? d_virial.as<double>() : nullptr, want_e ? d_scalars.as<double>() + 1 : nullptr, (T)kHartree2KcalMol);
+      c->launches++;
+    }
     // ---- (3) AEV backward: forces on local + ghost atoms, virial
     if (nlocal > 0) {
       const int acc_b = P.S * (P.nR + 1) + P.npairs * (P.ang_sub + 1);
@@ -815,35 +950,53 @@ struct Engine : EngineBase {
       auto launch2 = [&](auto kern, auto kern_strided) -> int {
         const int acc_b2 = aev2_bwd_acc_elems(P.S, P.nR, P.npairs, P.ang_sub);
         const Aev2Layout L2 = aev2_layout<T>(cap, capA, acc_b2, P.nZ, P.nA, true);
+        const Aev2Layout L1 = aev2_layout<T>(cap1, capA1, acc_b2, P.nZ, P.nA, true);
         const int smem2 = L2.bytes * kAev2Warps;
         ANIB_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem2));
+        ANIB_CUDA_OK(cudaFuncSetAttribute(kern_strided, cudaFuncAttributeMaxDynamicSharedMemorySize, smem2));
         const int grid = (nlocal + kAev2Warps - 1) / kAev2Warps;
-        Aev2Rows rs;
-        rs.range_flag = d_err.as<int>() + 1;
-        if (two_pass) {
-          const Aev2Layout L1 = aev2_layout<T>(cap1, capA1, acc_b2, P.nZ, P.nA, true);
-          rs.ovf_cnt = d_ovf.as<int>() + 3; rs.ovf_rows = d_ovf_rows.as<int>() + nlocal;
-          kern<<<grid, kAev2Warps * 32, L1.bytes * kAev2Warps, st>>>(
-              P, c->use_cuaev ? 1 : 0, d_x4.as<V4>(), d_beg.as<int64_t>(), d_cnt.as<int>(), jl(), d_order.as<int>(),
-              nlocal, d_daev.as<T>(), ld_aev, d_force.as<T>(), want_virial ? d_virial.as<double>() : nullptr,
-              (T)kHartree2KcalMol, cap1, capA1, L1.bytes, rs);
-          c->launches++;
-          rs = Aev2Rows();
+        auto go = [&](bool direct, int g, bool small, Aev2Rows rs) {
+          const int cp = small ? cap1 : cap, cpA = small ? capA1 : capA, lb = small ? L1.bytes : L2.bytes;
           rs.range_flag = d_err.as<int>() + 1;
-          rs.sel_cnt = d_ovf.as<int>() + 3; rs.sel_rows = d_ovf_rows.as<int>() + nlocal;
+          if (direct)
+            kern<<<g, kAev2Warps * 32, lb * kAev2Warps, st>>>(
+                P, c->use_cuaev ? 1 : 0, d_x4.as<V4>(), d_beg.as<int64_t>(), d_cnt.as<int>(), jl(), d_order.as<int>(),
+                nlocal, d_daev.as<T>(), ld_aev, d_force.as<T>(), want_virial ? d_virial.as<double>() : nullptr,
+                (T)kHartree2KcalMol, cp, cpA, lb, rs);
+          else
+            kern_strided<<<g, kAev2Warps * 32, lb * kAev2Warps, st>>>(
+                P, c->use_cuaev ? 1 : 0, d_x4.as<V4>(), d_beg.as<int64_t>(), d_cnt.as<int>(), jl(), d_order.as<int>(),
+                nlocal, d_daev.as<T>(), ld_aev, d_force.as<T>(), want_virial ? d_virial.as<double>() : nullptr,
+                (T)kHartree2KcalMol, cp, cpA, lb, rs);
+          c->launches++;
+        };
+        // a segment: its rows with the small buffers, then the rows that did not fit (deferred to list `slot`)
+        auto segment = [&](bool direct, int g, const int* sel_cnt, const int* sel_rows, int slot) {
+          Aev2Rows rs;
+          rs.sel_cnt = sel_cnt; rs.sel_rows = sel_rows;
+          int* const ocnt = d_ovf.as<int>() + 3 + slot;
+          int* const orow = d_ovf_rows.as<int>() + (size_t)(1 + slot) * nlocal;
+          if (two_pass) { rs.ovf_cnt = ocnt; rs.ovf_rows = orow; }
+          go(direct, g, two_pass, rs);
+          if (two_pass) {
+            Aev2Rows r2;
+            r2.sel_cnt = ocnt; r2.sel_rows = orow;
+            go(false, std::min(grid, 592), false, r2);
+          }
+        };
+        if (overlap) {
+          // boundary rows first: with them every ghost force is final and can travel while the interior rows are done
+          if (rows_bnd > 0) segment(false, (rows_bnd + kAev2Warps - 1) / kAev2Warps, d_sel.as<int>() + 1, d_rows.as<int>() + rows_int, 0);
+          axpy_kernel<T, double><<<(unsigned)(((int64_t)nghost * 3 + 255) / 256), 256, 0, st>>>(
+              d_force.as<T>() + (size_t)nlocal * 3, (double*)f_dev + (size_t)nlocal * 3, (int64_t)nghost * 3);
+          c->launches++;
+          ANIB_CUDA_OK(cudaEventRecord(c->evh[2], st));
+          ANIB_CUDA_OK(cudaStreamWaitEvent(cs, c->evh[2], 0));
+          if (int rc = halo_reverse_exchange_on(*halo, (double*)f_dev, cs)) return rc;
+          if (rows_int > 0) segment(false, (rows_int + kAev2Warps - 1) / kAev2Warps, d_sel.as<int>(), d_rows.as<int>(), 1);
+        } else {
+          segment(true, grid, nullptr, nullptr, 0);
         }
-        if (two_pass) {
-          ANIB_CUDA_OK(cudaFuncSetAttribute(kern_strided, cudaFuncAttributeMaxDynamicSharedMemorySize, smem2));
-          kern_strided<<<std::min(grid, 592), kAev2Warps * 32, smem2, st>>>(
-              P, c->use_cuaev ? 1 : 0, d_x4.as<V4>(), d_beg.as<int64_t>(), d_cnt.as<int>(), jl(), d_order.as<int>(),
-              nlocal, d_daev.as<T>(), ld_aev, d_force.as<T>(), want_virial ? d_virial.as<double>() : nullptr,
-              (T)kHartree2KcalMol, cap, capA, L2.bytes, rs);
-        } else
-          kern<<<grid, kAev2Warps * 32, smem2, st>>>(
-              P, c->use_cuaev ? 1 : 0, d_x4.as<V4>(), d_beg.as<int64_t>(), d_cnt.as<int>(), jl(), d_order.as<int>(),
-              nlocal, d_daev.as<T>(), ld_aev, d_force.as<T>(), want_virial ? d_virial.as<double>() : nullptr,
-              (T)kHartree2KcalMol, cap, capA, L2.bytes, rs);
-        c->launches++;
         return 0;
       };
       int rc;
@@ -856,15 +1009,6 @@ struct Engine : EngineBase {
       else if (P.nZ == 2) rc = launch(aev_backward_kernel<T, 2>);
       else { set_error("unsupported number of ShfZ values (supported: 1, 2, 4, 8)"); return 1; }
       if (rc) return rc;
-    }
-    // ---- (3b) RepulsionXTB pair term (models with rep_calc): forces / virial into the same arrays, energy into scalars[1]
-    const bool want_e = out_energy != nullptr;
-    if (hm.use_repulsion && nlocal > 0) {
-      if (want_e) ANIB_CUDA_OK(cudaMemsetAsync(d_scalars.as<double>() + 1, 0, sizeof(double), st));
-      repulsion_kernel<T><<<(unsigned)(((int64_t)nlocal * 32 + 255) / 256), 256, 0, st>>>(
-          rep, d_x4.as<V4>(), d_beg.as<int64_t>(), d_cnt.as<int>(), jl(), nlocal, d_force.as<T>(),
-          want_virial ? d_virial.as<double>() : nullptr, want_e ? d_scalars.as<double>() + 1 : nullptr, (T)kHartree2KcalMol);
-      c->launches++;
     }
     if (tm) cudaEventRecord(c->ev[4], st);
     // ---- (4) reductions and outputs
@@ -888,10 +1032,21 @@ struct Engine : EngineBase {
       c->launches++;
     }
     if (f_dev != nullptr && ntotal > 0) {
-      const int64_t n3 = (int64_t)ntotal * 3;
+      const int64_t n3 = (int64_t)(overlap ? nlocal : ntotal) * 3;      // (overlapped exchange: the ghosts' share has left already)
       if (f_is_float) axpy_kernel<T, float><<<(unsigned)((n3 + 255) / 256), 256, 0, st>>>(d_force.as<T>(), (float*)f_dev, n3);
       else axpy_kernel<T, double><<<(unsigned)((n3 + 255) / 256), 256, 0, st>>>(d_force.as<T>(), (double*)f_dev, n3);
       c->launches++;
+    }
+    if (overlap) {
+      // the ghost forces that came back are added once the local forces are in place, and the step's stream waits for that
+      ANIB_CUDA_OK(cudaEventRecord(c->evh[3], st));
+      ANIB_CUDA_OK(cudaStreamWaitEvent(cs, c->evh[3], 0));
+      if (int rc = halo_reverse_unpack_on(*halo, (double*)f_dev, cs)) return rc;
+      ANIB_CUDA_OK(cudaEventRecord(c->evh[4], cs));
+      ANIB_CUDA_OK(cudaStreamWaitEvent(st, c->evh[4], 0));
+    } else if (halo) {
+      if (int rc = halo_reverse_exchange_on(*halo, (double*)f_dev, st)) return rc;
+      if (int rc = halo_reverse_unpack_on(*halo, (double*)f_dev, st)) return rc;
     }
     // ---- D2H
     bool need_sync = false;
@@ -1150,6 +1305,8 @@ void ani_ctx_destroy(ani_ctx* c) {
   cudaSetDevice(c->device);
   c->eng.reset();
   for (void* q : c->pinned_host) { cudaHostUnregister(q); cudaGetLastError(); }
+  for (int q = 0; q < 5; q++) if (c->evh[q]) cudaEventDestroy(c->evh[q]);
+  if (c->comm_stream) cudaStreamDestroy(c->comm_stream);
   if (c->d_word) cudaFree(c->d_word);
   if (c->h_word) cudaFreeHost(c->h_word);
   for (int q = 0; q < 6; q++) if (c->ev[q]) cudaEventDestroy(c->ev[q]);
@@ -1189,6 +1346,7 @@ int ani_ctx_set_option(ani_ctx* c, const char* name, int value) {
   if (!strcmp(name, "mlp_fused")) c->opt_mlp_fused = value != 0;
   else if (!strcmp(name, "fused_prof")) c->opt_fused_prof = value != 0;
   else if (!strcmp(name, "gemm_ctas")) c->opt_gemm_ctas = value > 0 ? value : 0;
+  else if (!strcmp(name, "halo_overlap")) c->opt_halo_overlap = value != 0;
   else if (!strcmp(name, "aev_two_pass")) c->opt_aev_two_pass = value != 0;
   else if (!strcmp(name, "pin_user")) { c->opt_pin_user = value != 0; if (!value && c->eng) c->eng->release_pins(); }
   else { set_error(std::string("ani_ctx_set_option: unknown option '") + name + "'"); return 1; }
@@ -1665,59 +1823,27 @@ void ani_halo_plan_destroy(ani_halo_plan* hp) {
 // ghost positions: x[nlocal + ...] <- owners' x (+ periodic shift), blocks ordered by source rank
 int ani_halo_forward(ani_halo_plan* hp, double* x_dev) {
   if (!hp || !x_dev) { set_error("ani_halo_forward: null argument"); return 1; }
-  HaloPlan& p = hp->p;
-  cudaStream_t st = hp->ctx->stream;
-  ANIB_CUDA_OK(cudaSetDevice(p.device));
-  if (p.nsend > 0) {
-    halo_pack_kernel<double><<<(unsigned)((p.nsend * 3 + 255) / 256), 256, 0, st>>>(x_dev, p.d_send_index, p.d_send_shift, p.nsend, p.d_send_buf);
-    ANIB_CUDA_OK(cudaGetLastError());
-  }
-  double* ghosts = x_dev + (size_t)p.nlocal * 3;
-  const int64_t self = p.send_off[p.rank + 1] - p.send_off[p.rank];
-  if (self > 0)       // periodic self images: a device copy, no communication
-    ANIB_CUDA_OK(cudaMemcpyAsync(ghosts + p.recv_off[p.rank] * 3, p.d_send_buf + p.send_off[p.rank] * 3, (size_t)self * 3 * sizeof(double),
-                                 cudaMemcpyDeviceToDevice, st));
-  if (p.nranks > 1) {
-    NcclApi& n = nccl_api();
-    ANIB_NCCL_OK(n.GroupStart());
-    for (int r = 0; r < p.nranks; r++) {
-      if (r == p.rank) continue;
-      const int64_t ns = p.send_off[r + 1] - p.send_off[r], nr = p.recv_off[r + 1] - p.recv_off[r];
-      if (ns > 0) ANIB_NCCL_OK(n.Send(p.d_send_buf + p.send_off[r] * 3, (size_t)ns * 3, ncclDouble, r, p.comm, st));
-      if (nr > 0) ANIB_NCCL_OK(n.Recv(ghosts + p.recv_off[r] * 3, (size_t)nr * 3, ncclDouble, r, p.comm, st));
-    }
-    ANIB_NCCL_OK(n.GroupEnd());
-  }
-  return 0;
+  ANIB_CUDA_OK(cudaSetDevice(hp->p.device));
+  return halo_forward_on(hp->p, x_dev, hp->ctx->stream);
 }
 
 // ghost forces: f[owner] += f[ghost]   (newton off: the pair style folds its own ghost forces, pair_ani.cpp:197-201)
 int ani_halo_reverse(ani_halo_plan* hp, double* f_dev) {
   if (!hp || !f_dev) { set_error("ani_halo_reverse: null argument"); return 1; }
-  HaloPlan& p = hp->p;
-  cudaStream_t st = hp->ctx->stream;
-  ANIB_CUDA_OK(cudaSetDevice(p.device));
-  double* ghosts = f_dev + (size_t)p.nlocal * 3;
-  const int64_t self = p.send_off[p.rank + 1] - p.send_off[p.rank];
-  if (self > 0)
-    ANIB_CUDA_OK(cudaMemcpyAsync(p.d_send_buf + p.send_off[p.rank] * 3, ghosts + p.recv_off[p.rank] * 3, (size_t)self * 3 * sizeof(double),
-                                 cudaMemcpyDeviceToDevice, st));
-  if (p.nranks > 1) {
-    NcclApi& n = nccl_api();
-    ANIB_NCCL_OK(n.GroupStart());
-    for (int r = 0; r < p.nranks; r++) {
-      if (r == p.rank) continue;
-      const int64_t ns = p.send_off[r + 1] - p.send_off[r], nr = p.recv_off[r + 1] - p.recv_off[r];
-      if (nr > 0) ANIB_NCCL_OK(n.Send(ghosts + p.recv_off[r] * 3, (size_t)nr * 3, ncclDouble, r, p.comm, st));
-      if (ns > 0) ANIB_NCCL_OK(n.Recv(p.d_send_buf + p.send_off[r] * 3, (size_t)ns * 3, ncclDouble, r, p.comm, st));
-    }
-    ANIB_NCCL_OK(n.GroupEnd());
-  }
-  if (p.nsend > 0) {
-    halo_unpack_add_kernel<double><<<(unsigned)((p.nsend * 3 + 255) / 256), 256, 0, st>>>(f_dev, p.d_send_index, p.d_send_buf, p.nsend);
-    ANIB_CUDA_OK(cudaGetLastError());
-  }
-  return 0;
+  ANIB_CUDA_OK(cudaSetDevice(hp->p.device));
+  if (int rc = halo_reverse_exchange_on(hp->p, f_dev, hp->ctx->stream)) return rc;
+  return halo_reverse_unpack_on(hp->p, f_dev, hp->ctx->stream);
+}
+
+// One domain-decomposed step: ghost positions from their owners, energy / forces, ghost forces back to their owners --
+// ani_halo_forward + ani_compute_device + ani_halo_reverse in one call, which lets the library run the exchange on a second
+// stream under the interior atoms' share of the AEV kernels (option "halo_overlap", default 1; needs a device-built list).
+int ani_compute_device_halo(ani_ctx* c, ani_halo_plan* hp, double* x_dev, double* f_dev, double* eatom_dev, double* out_energy,
+                            double* out_virial9) {
+  if (!c || !hp || !x_dev || !f_dev) { set_error("ani_compute_device_halo: null argument"); return 1; }
+  if (hp->ctx != c) { set_error("ani_compute_device_halo: the plan belongs to another context"); return 1; }
+  ANIB_CUDA_OK(cudaSetDevice(c->device));
+  return c->eng->compute(x_dev, true, false, out_energy, nullptr, f_dev, false, nullptr, eatom_dev, out_virial9, &hp->p);
 }
 
 int ani_halo_pack_x(ani_ctx* c, const void* x_dev, int is_float, const int64_t* send_index_dev, const void* shift_dev,

@@ -93,24 +93,44 @@ __global__ void nb_search_kernel(const double* __restrict__ x, int nlocal, NbGri
   if (!FILL) cnt[i] = n;
 }
 
-// Species bookkeeping of a rebuild on the device (the host used to loop five times over the atoms): histogram of the local
-// atoms' species, the set of species present among local + ghost atoms, and a flag for indices outside the model.
-// stats: [0..7] histogram, [8] present mask, [9] invalid flag
+// Species bookkeeping of a rebuild on the device (the host used to loop five times over the atoms): the sort key of every local
+// atom, 2 * species + (1 if it has a ghost neighbour: a BOUNDARY atom), the histogram of the keys, the set of species present
+// among local + ghost atoms, and a flag for indices outside the model.  Rows sorted by this key are bucketed by species with
+// the interior atoms first in each bucket: their AEVs do not depend on ghost positions (and no ghost force comes from them),
+// which is what lets the halo exchange overlap their share of the AEV kernels.
+// stats: [0..15] histogram of the keys, [16] present mask, [17] invalid flag
+constexpr int kNbStats = 18;
 struct NbSpeciesMap { int cmap[8]; };
-__global__ void nb_species_stats_kernel(const int* __restrict__ species, int nlocal, int ntotal, int S, int* __restrict__ stats) {
-  __shared__ int sh[10];
-  if (threadIdx.x < 10) sh[threadIdx.x] = 0;
+__global__ void nb_species_stats_kernel(const int* __restrict__ species, const int* __restrict__ bnd, int nlocal, int ntotal, int S,
+                                        int* __restrict__ key, int* __restrict__ stats) {
+  __shared__ int sh[kNbStats];
+  if (threadIdx.x < kNbStats) sh[threadIdx.x] = 0;
   __syncthreads();
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < ntotal; i += gridDim.x * blockDim.x) {
     const int s = species[i];
-    if (s < 0 || s >= S) { sh[9] = 1; continue; }
-    if (i < nlocal) atomicAdd(&sh[s], 1);
-    if (!((sh[8] >> s) & 1)) atomicOr(&sh[8], 1 << s);
+    if (s < 0 || s >= S) { sh[17] = 1; if (i < nlocal) key[i] = 0; continue; }
+    if (i < nlocal) {
+      const int k = 2 * s + (bnd[i] != 0 ? 1 : 0);
+      key[i] = k;
+      atomicAdd(&sh[k], 1);
+    }
+    atomicOr(&sh[16], 1 << s);
   }
   __syncthreads();
-  if (threadIdx.x < 8 && sh[threadIdx.x]) atomicAdd(&stats[threadIdx.x], sh[threadIdx.x]);
-  if (threadIdx.x == 8 && sh[8]) atomicOr(&stats[8], sh[8]);
-  if (threadIdx.x == 9 && sh[9]) atomicOr(&stats[9], 1);
+  if (threadIdx.x < 16 && sh[threadIdx.x]) atomicAdd(&stats[threadIdx.x], sh[threadIdx.x]);
+  if (threadIdx.x == 16 && sh[16]) atomicOr(&stats[16], sh[16]);
+  if (threadIdx.x == 17 && sh[17]) atomicOr(&stats[17], 1);
+}
+// rows (positions in the sorted order) of the interior atoms, then of the boundary atoms: list[0 .. n_int), list[n_int .. nlocal)
+struct NbRowSplit { int boff[9], nint[8], int_before[8], bnd_before[8], n_int, S; };
+__global__ void nb_row_lists_kernel(NbRowSplit sp, int nlocal, int* __restrict__ list) {
+  const int r = blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= nlocal) return;
+  int s = 0;
+  while (s + 1 < sp.S && r >= sp.boff[s + 1]) s++;
+  const int k = r - sp.boff[s];
+  if (k < sp.nint[s]) list[sp.int_before[s] + k] = r;
+  else list[sp.n_int + sp.bnd_before[s] + (k - sp.nint[s])] = r;
 }
 // compact species index of every atom (the kernels' species), and the sort key of the local atoms
 __global__ void nb_species_compact_kernel(const int* __restrict__ species, int ntotal, NbSpeciesMap m, int* __restrict__ cspecies) {
@@ -150,7 +170,7 @@ template <int MODE>
 __global__ void nb_search_warp_kernel(const double* __restrict__ xs, const double* __restrict__ ys, const double* __restrict__ zs,
                                       const float4* __restrict__ pk, int ntotal, int nlocal, NbGrid G, const int* __restrict__ cell_beg,
                                       const int* __restrict__ cell_end, double cut2, float eps, int* __restrict__ cnt,
-                                      const int64_t* __restrict__ beg, int stride, int* __restrict__ jlist) {
+                                      int* __restrict__ bnd, const int64_t* __restrict__ beg, int stride, int* __restrict__ jlist) {
   const int w = (int)(((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5), lane = threadIdx.x & 31;
   if (w >= ntotal) return;
   const float4 pi = pk[w];
@@ -163,6 +183,7 @@ __global__ void nb_search_warp_kernel(const double* __restrict__ xs, const doubl
   const int cz = nb_cell_coord(zs[w], G.lo[2], G.inv_cell, G.n[2]);
   const unsigned lt = (1u << lane) - 1u;
   int n = 0;
+  bool ghost_nb = false;                          // a neighbour of this atom is a ghost (index >= nlocal)
   int* out = MODE == 1 ? jlist + beg[i] : MODE == 2 ? jlist + (size_t)i * stride : nullptr;
   const int room = MODE == 2 ? stride : 0x7fffffff;
   for (int dz = -1; dz <= 1; dz++) {
@@ -196,6 +217,7 @@ __global__ void nb_search_warp_kernel(const double* __restrict__ xs, const doubl
           hit = hit && j != i;
         }
         const unsigned m = __ballot_sync(0xffffffffu, hit);
+        if (MODE != 1) ghost_nb |= __any_sync(0xffffffffu, hit && j >= nlocal);
         if (MODE != 0 && hit) {
           const int pos = n + __popc(m & lt);
           if (pos < room) out[pos] = j;
@@ -204,7 +226,7 @@ __global__ void nb_search_warp_kernel(const double* __restrict__ xs, const doubl
       }
     }
   }
-  if (MODE != 1 && lane == 0) cnt[i] = n;
+  if (MODE != 1 && lane == 0) { cnt[i] = n; bnd[i] = ghost_nb ? 1 : 0; }
 }
 
 }  // namespace anib

@@ -136,5 +136,21 @@ class GpuDomainStep(DomainStep):
         e, _ = self.ani.compute_device(self.x.data_ptr(), False, self.f.data_ptr(), False, 0, want_energy=want_energy)
         return e
 
+    def use_device_list(self, cutoff: float):
+        """Replace the host-built list by one built on the device from the current positions (ani_build_neighbors).  Besides
+        being what an MD run does on rebuild steps, a device-built list carries the interior / boundary split of the local
+        atoms that lets the library overlap the ghost exchange with the interior atoms' AEV kernels."""
+        self.forward_halo()
+        lo = (self.x.min(0).values - 1e-6).cpu().numpy()
+        hi = (self.x.max(0).values + 1e-6).cpu().numpy()
+        return self.ani.build_neighbors(self.sub.species, None, self.nlocal, cutoff, lo=lo, hi=hi, x_dev_ptr=self.x.data_ptr())
+
     def step_gpu(self, want_energy: bool = False):
+        """One step through ani_compute_device_halo: ghost positions in, forces, ghost forces back -- one library call."""
+        self.f.zero_()                               # Verlet::force_clear
+        e, _ = self.ani.compute_device_halo(self.plan, self.x.data_ptr(), self.f.data_ptr(), want_energy=want_energy)
+        return e
+
+    def step_gpu_serial(self, want_energy: bool = False):
+        """The same step as three library calls (exchange, compute, exchange) on one stream: the reference for the fused call."""
         return self.step(lambda s: s.pair_compute(want_energy))

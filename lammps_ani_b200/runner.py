@@ -76,6 +76,7 @@ def load_library():
     L.ani_halo_plan_destroy.argtypes = [vp]
     L.ani_halo_plan_destroy.restype = None
     L.ani_halo_forward.argtypes = [vp, vp]
+    L.ani_compute_device_halo.argtypes = [vp, vp, vp, vp, vp, vp, vp]
     L.ani_halo_reverse.argtypes = [vp, vp]
     L.ani_halo_pack_x.argtypes = [vp, vp, i32, vp, vp, i64, vp]
     L.ani_halo_unpack_add_f.argtypes = [vp, vp, i32, vp, vp, i64]
@@ -85,7 +86,7 @@ def load_library():
                  "ani_compute_device", "ani_debug_get_aev", "ani_halo_pack_x", "ani_halo_unpack_add_f", "ani_build_neighbors",
                  "ani_debug_get_neighbors", "ani_md_nve_initial", "ani_md_nve_final", "ani_md_langevin", "ani_md_sum_mv2", "ani_md_sum_mv2_static", "ani_md_max_disp2", "ani_ctx_pin_host",
                  "ani_md_ghost_x", "ani_md_fold_ghost_f", "ani_halo_unique_id", "ani_halo_plan_create", "ani_halo_forward",
-                 "ani_halo_reverse"):
+                 "ani_halo_reverse", "ani_compute_device_halo"):
         getattr(L, name).restype = i32
     _lib = L
     return L
@@ -99,7 +100,7 @@ EXPORTED_SYMBOLS = [
     "ani_device_count", "ani_build_neighbors", "ani_debug_get_neighbors", "ani_ctx_release_host_buffers", "ani_ctx_set_option",
     "ani_md_nve_initial", "ani_md_nve_final", "ani_md_langevin", "ani_md_sum_mv2", "ani_md_sum_mv2_static", "ani_md_max_disp2", "ani_ctx_pin_host", "ani_md_ghost_x", "ani_md_fold_ghost_f",
     "ani_dev_alloc", "ani_dev_free", "ani_dev_upload", "ani_dev_download", "ani_dev_zero",
-    "ani_halo_unique_id", "ani_halo_plan_create", "ani_halo_plan_destroy", "ani_halo_forward", "ani_halo_reverse",
+    "ani_halo_unique_id", "ani_halo_plan_create", "ani_halo_plan_destroy", "ani_halo_forward", "ani_halo_reverse", "ani_compute_device_halo",
 ]
 
 
@@ -286,6 +287,15 @@ class ANI:
         _check(self._L.ani_compute_device(self._ctx, C.c_void_p(x_ptr), int(x_is_float), C.c_void_p(f_ptr),
                                           int(f_is_float), C.c_void_p(eatom_ptr or 0),
                                           C.addressof(energy) if want_energy else None, _ptr(virial)))
+        return (energy.value if want_energy else None), (virial.reshape(3, 3) if want_virial else None)
+
+    def compute_device_halo(self, plan, x_ptr: int, f_ptr: int, eatom_ptr: int = 0, want_energy: bool = True, want_virial: bool = False):
+        """ani_halo_forward + ani_compute_device + ani_halo_reverse in one call (x, f: device arrays of doubles); the library
+        overlaps the exchange with the interior atoms' AEV kernels when the list was built on the device."""
+        energy = C.c_double()
+        virial = np.empty(9, dtype=np.float64) if want_virial else None
+        _check(self._L.ani_compute_device_halo(self._ctx, plan, C.c_void_p(x_ptr), C.c_void_p(f_ptr), C.c_void_p(eatom_ptr or 0),
+                                               C.addressof(energy) if want_energy else None, _ptr(virial)))
         return (energy.value if want_energy else None), (virial.reshape(3, 3) if want_virial else None)
 
     # ---- device-resident integration (fix nve / fix langevin on the GPU; include/ani_b200.h ani_md_*): raw device pointers

@@ -369,3 +369,48 @@ def test_library_halo_plan_matches_torch_reference(ANI, ani2x_synth_path):
     g.forward_halo_local(); c.forward_halo()
     ani.synchronize()
     assert (g.x.cpu() - c.x).abs().max() < 1e-12
+
+
+@pytest.mark.parametrize("repulsion", [False, True])
+def test_overlapped_halo_step_matches_serial(ANI, ani2x_synth_path, ani1xnr_path, tmp_path, repulsion):
+    """ani_compute_device_halo (exchange on a second stream under the interior atoms' AEV kernels; needs the device-built list's
+    interior / boundary split) against the same step as three serial calls, with the host-installed list (always serial), and
+    with the overlap switched off: forces within the fp32 summation-order noise, energy within 1e-9 relative.  One rank: every
+    ghost is a periodic self image, so the exchange is device copies -- the stream / event choreography and the split of the AEV
+    launches are what is exercised (bench.py's multi-GPU force check covers the NCCL leg)."""
+    import torch
+    from lammps_ani_b200 import aniw, ddstep, extract
+    path = ani2x_synth_path
+    if repulsion:
+        path = str(tmp_path / "ani1x_nr_repulsion.aniw")
+        aniw.save(extract.with_repulsion(aniw.load(ani1xnr_path)), path)
+        x, sp, box = domain.make_combustion_box(3000, seed=5)
+    else:
+        x, sp, box = domain.make_water_box((8, 7, 7), seed=4)
+    sub = domain.decompose(x, sp, box)[0]
+    halo = domain.replica_halo(sub, box, (1, 1, 1), 0)
+    il, nn, jl = domain.full_neighbor_list(sub.x, sub.nlocal)
+    ani = ANI(path, 0, -1, True, True, True)
+    dev = torch.device("cuda", 0)
+    g = ddstep.GpuDomainStep(ani, sub, halo, dev, il, nn, jl)
+    nl = sub.nlocal
+
+    def run(fn):
+        out = []
+        for _ in range(3):                                   # (the third step runs the two-pass AEV configuration)
+            e = fn(True)
+            ani.synchronize()
+            out.append((e, g.f[:nl].cpu().numpy().copy()))
+        return out[-1]
+
+    e_ref, f_ref = run(g.step_gpu_serial)                    # host list, three calls
+    e_h, f_h = run(g.step_gpu)                               # host list, one call (serialised inside: no split known)
+    g.use_device_list(7.1)
+    e_o, f_o = run(g.step_gpu)                               # device list: overlapped
+    ani.set_option("halo_overlap", 0)
+    e_s, f_s = run(g.step_gpu)                               # device list, overlap off
+    ani.set_option("halo_overlap", 1)
+    for e, f in ((e_h, f_h), (e_o, f_o), (e_s, f_s)):
+        assert abs(e - e_ref) <= 1e-9 * abs(e_ref)
+        assert np.abs(f - f_ref).max() <= 2e-3               # kcal/mol/A: 1e-4 eV/A
+    assert np.abs(f_ref).max() > 1.0
