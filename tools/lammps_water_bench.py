@@ -97,6 +97,9 @@ def main():
         keep = [ln for ln in out.splitlines() if any(k in ln for k in ("Loop time", "Performance", "Pair  ", "Neigh ", "Comm  ", "Modify", "Output",
                                                                       "Other ", "Neighbor list builds", "Step ", "atoms", "ERROR", "Ave neighs"))]
         print("\n".join(keep[-40:]))
+        prof = [ln for ln in r.stderr.splitlines() if ln.startswith("[")]          # library profiling lines (ANI_B200_*_PROF)
+        if prof:
+            print("\n".join(prof[-30:]))
         if r.returncode != 0:
             print(out[-3000:], r.stderr[-2000:])
         loops = [ln for ln in out.splitlines() if ln.startswith("Loop time")]
