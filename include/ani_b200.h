@@ -71,7 +71,8 @@ int ani_ctx_synchronize(ani_ctx* ctx);
  * "pin_user" 1 (default 0): page-lock caller x / out_force arrays seen at a stable address and DMA from / to them
  * directly -- the caller then must call ani_ctx_release_host_buffers before freeing or reallocating them (pair style, bench);
  * "aev_two_pass" 1 (default) / 0; "gemm_ctas" n > 0: cap the persistent GEMM grids at n CTAs; "fused_prof" 1: print the
- * fused kernel's cycle counters to stderr.  The environment (ANI_B200_FUSED, ANI_B200_AEV_TWO_PASS, ANI_B200_GEMM_CTAS,
+ * fused kernel's cycle counters to stderr; "halo_overlap" 1 (default) / 0: ani_compute_device_halo may run the ghost exchange on
+ * a second stream under the interior atoms' AEV kernels.  The environment (ANI_B200_FUSED, ANI_B200_AEV_TWO_PASS, ANI_B200_GEMM_CTAS,
  * ANI_B200_FUSED_PROF) only sets the defaults a context starts with. */
 int ani_ctx_set_option(ani_ctx* ctx, const char* name, int value);
 /* Page-lock a caller array (cudaHostRegister) so that ani_dev_upload / ani_dev_download / ani_compute on it are direct DMA

@@ -166,7 +166,7 @@ class ANI:
         _check(self._L.ani_ctx_set_mlp_mode(self._ctx, mode))
 
     def set_option(self, name: str, value: int):
-        """Per-context switch (include/ani_b200.h: "mlp_fused", "pin_user", "aev_two_pass", "gemm_ctas", "fused_prof")."""
+        """Per-context switch (include/ani_b200.h: "mlp_fused", "pin_user", "aev_two_pass", "gemm_ctas", "fused_prof", "halo_overlap")."""
         _check(self._L.ani_ctx_set_option(self._ctx, name.encode(), int(value)))
 
     def release_host_buffers(self):
