@@ -12,6 +12,7 @@
 #include "fix_ani_md.h"
 
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 
 #include "ani_b200.h"
@@ -23,6 +24,7 @@
 #include "neighbor.h"
 #include "output.h"
 #include "pair_ani.h"
+#include "platform.h"
 #include "update.h"
 
 using namespace LAMMPS_NS;
@@ -69,6 +71,8 @@ void FixANIMD::init() {
 }
 
 void FixANIMD::upload_state() {
+  static const bool prof = getenv("LAMMPS_ANI_PROFILING") != nullptr;
+  const double t0 = prof ? platform::walltime() : 0.0;
   ani_ctx* c = pair->context();
   const int n = atom->nlocal;
   if (n > cap) {
@@ -86,15 +90,19 @@ void FixANIMD::upload_state() {
       ani_dev_upload(c, tag_dev, h_tag.data(), (size_t)n * sizeof(long long)))
     error->one(FLERR, "fix ani/md: upload failed: {}", ani_last_error());
   uploaded_step = pair->res.rebuilt_step;
+  if (prof) fprintf(stderr, "[fix ani/md] v / mass / tag upload after a rebuild %.3f ms\n", (platform::walltime() - t0) * 1e3);
 }
 
 void FixANIMD::sync_host(bool with_forces) {
   if (!pair->res.valid || uploaded_step != pair->res.rebuilt_step) return;     // the host arrays are the current state
+  static const bool prof = getenv("LAMMPS_ANI_PROFILING") != nullptr;
+  const double t0 = prof ? platform::walltime() : 0.0;
   pair->download_x();
   if (atom->nlocal > 0 && ani_dev_download(pair->context(), &atom->v[0][0], v_dev, (size_t)atom->nlocal * 3 * sizeof(double)))
     error->one(FLERR, "fix ani/md: download failed: {}", ani_last_error());
   if (with_forces) pair->download_f();
   host_current = true;
+  if (prof) fprintf(stderr, "[fix ani/md] x / v%s to the host (waits for the queued steps) %.3f ms\n", with_forces ? " / f" : "", (platform::walltime() - t0) * 1e3);
 }
 
 /* Verlet::setup has just evaluated the forces from the host positions (the pair style uploaded x and built the list):

@@ -20,6 +20,7 @@
 #include "memory.h"
 #include "neigh_list.h"
 #include "neighbor.h"
+#include "platform.h"
 #include "domain.h"
 #include "comm.h"
 #include "update.h"
@@ -219,7 +220,11 @@ void PairANIB200::download_f() {
 void PairANIB200::resident_compute(int eflag, int vflag) {
   const int nlocal = atom->nlocal, nghost = atom->nghost, ntotal = nlocal + nghost;
   double** x = atom->x;
+  // LAMMPS_ANI_PROFILING (the reference's switch, pair_ani.cpp:49): wall time of the phases of a rebuild step, to stderr
+  static const bool prof = getenv("LAMMPS_ANI_PROFILING") != nullptr;
+  double tp[5] = {0, 0, 0, 0, 0};
   if (neighbor->ago == 0 || !res.valid) {
+    if (prof) tp[0] = platform::walltime();
     // LAMMPS's per-atom arrays are pageable: page-lock them once per allocation so the rebuild-step transfers are direct DMA
     if (atom->nmax != last_nmax) {
       ani_ctx_release_host_buffers(ctx);
@@ -261,6 +266,7 @@ void PairANIB200::resident_compute(int eflag, int vflag) {
       h_owner[g] = o;
       for (int d = 0; d < 3; d++) h_shift[3 * (size_t)g + d] = x[nlocal + g][d] - x[o][d];
     }
+    if (prof) tp[1] = platform::walltime();
     if (ani_dev_upload(ctx, res.x, ntotal > 0 ? &x[0][0] : nullptr, (size_t)ntotal * 3 * sizeof(double)) ||
         ani_dev_upload(ctx, res.x0, nlocal > 0 ? &x[0][0] : nullptr, (size_t)nlocal * 3 * sizeof(double)) ||
         ani_dev_upload(ctx, res.owner, h_owner.data(), (size_t)nghost * sizeof(int)) ||
@@ -272,8 +278,14 @@ void PairANIB200::resident_compute(int eflag, int vflag) {
       hi[d] = domain->subhi[d] + comm->cutghost[d];
     }
     int64_t np = 0;
+    if (prof) tp[2] = platform::walltime();
     if (ani_build_neighbors(ctx, nlocal, ntotal, species.data(), res.x, 1, neighbor->cutneighmax, lo, hi, &np))
       fail("device neighbour build failed");
+    if (prof) {
+      tp[3] = platform::walltime();
+      fprintf(stderr, "[pair ani rebuild] host index work %.3f ms | uploads (x, x0, owners, shifts) %.3f | device list %.3f | %d local + %d ghost atoms\n",
+              (tp[1] - tp[0]) * 1e3, (tp[2] - tp[1]) * 1e3, (tp[3] - tp[2]) * 1e3, nlocal, nghost);
+    }
     npairs = np;
     res.nlocal = nlocal; res.nghost = nghost;
     res.valid = true;
